@@ -1,0 +1,270 @@
+#!/usr/bin/env python3
+"""bench.py -- SGD row*iterations/s of the per-micro-batch learning path on N B200s.
+
+A "step" is one micro-batch: the hot path (numIterations fused SGD-iteration passes + their
+fixed-order reduce/update) over a synthetic dense micro-batch already resident in HBM.
+
+  python bench.py --gpus N --steps K --warmup W            (N > 1: launched under torchrun)
+  python bench.py --impl reference ...                      (the CPU restatement, all host cores)
+
+Workloads (BASELINE.json configs):
+  dense_1m    2^20 rows/GPU x 1004 features, 20 iterations  (configs[1]; the default)
+  dense_16m   2^24 rows/GPU x 1004 features, 50 iterations  (configs[2], HBM-roofline config; no e2e:
+              134.75 GB does not stage through host memory)
+Multi-GPU: every rank holds the same number of rows (weak scaling); per iteration the ranks exchange
+their (gradSum, lossSum, count) shard vectors with one NCCL all-gather.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    "dense_1m": dict(rows=1 << 20, d=1004, iters=20, step=0.1),
+    "dense_16m": dict(rows=1 << 24, d=1004, iters=50, step=0.1),
+}
+METRIC = "sgd_row_iterations_per_s"
+UNIT = "row*iter/s"
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        sm = sorted(float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit())
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 3 + i and r[3 + i].lower() == "active" for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+def cpu_leg(wl, steps, warmup, budget_s=15.0):
+    """The CPU restatement (oracle/twtml_oracle.c, OpenMP over row partitions like Spark local[N]) on a
+    bounded sample of the workload: same width, same iteration count, fewer rows."""
+    from oracle import oracle_c
+    import numpy as np
+    oracle_c.build()
+    cores = oracle_c.max_threads()
+    d, iters = wl["d"], wl["iters"]
+    rows = 1 << 17
+    X, y = oracle_c.synth_dense(rows, d, seed=42)
+    w0 = np.zeros(d)
+    kw = dict(X=X, step_size=wl["step"], num_iterations=iters, convergence_tol=0.0, partitions=cores, threads=cores)
+    t0 = time.perf_counter()
+    oracle_c.sgd(y, d, w0, **kw)                       # also the first warm-up step
+    once = time.perf_counter() - t0
+    warm = max(0, warmup - 1)
+    k = max(1, min(steps, int(budget_s / max(once, 1e-3))))
+    for _ in range(min(warm, 2)):
+        oracle_c.sgd(y, d, w0, **kw)
+    t0 = time.perf_counter()
+    for _ in range(k):
+        oracle_c.sgd(y, d, w0, **kw)
+    dt = time.perf_counter() - t0
+    value = rows * iters * k / dt
+    sample = "%d of %d rows x %d features, %d iterations, %d steps, OpenMP static row partitions on %d threads" % (
+        rows, wl["rows"], d, iters, k, cores)
+    return dict(value=value, unit=UNIT, cores=cores, kind="port", sample=sample), dt / k * 1e3, k
+
+
+def run_reference(args, wl):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cb, ms, k = cpu_leg(wl, args.steps, args.warmup)
+    line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": k,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": args.workload, "rows_per_gpu": wl["rows"], "features": wl["d"], "sgd_iterations": wl["iters"],
+                       "note": "CPU restatement of the reference's MLlib 1.6.1 path (the Scala/Spark reference cannot run here: no JVM)"},
+            "cpu_baseline": cb, "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="dense_1m", choices=sorted(WORKLOADS))
+    ap.add_argument("--rows", type=int, default=0, help="override rows per GPU (testing)")
+    ap.add_argument("--iters", type=int, default=0, help="override SGD iterations per micro-batch (testing)")
+    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    wl = dict(WORKLOADS[args.workload])
+    if args.rows:
+        wl["rows"] = args.rows
+    if args.iters:
+        wl["iters"] = args.iters
+    if args.impl == "reference":
+        return run_reference(args, wl)
+    if args.warmup < 3:
+        args.warmup = 3
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    import twtml_b200 as tw
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit("--gpus %d but WORLD_SIZE=%d: launch N > 1 with torch.distributed.run" % (args.gpus, world))
+    torch.cuda.set_device(local)
+    nccl_id = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        ids = [tw.Context.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0)
+        nccl_id = ids[0]
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    n, d, iters = wl["rows"], wl["d"], wl["iters"]
+    ctx = tw.Context(local, rank, world, nccl_id)
+    ctx.profile(True)
+    model = (tw.StreamingLinearRegressionWithSGD(ctx=ctx).setNumIterations(iters).setStepSize(wl["step"])
+             .setMiniBatchFraction(1.0).setConvergenceTol(0.0).setInitialWeights(tw.Vectors.zeros(d)))
+    batch = ctx.batch_synth_dense(n, d, seed=42, row0=rank * n)      # resident in HBM before the timed region
+
+    for _ in range(args.warmup):
+        model.trainOnBatch(batch)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    dev_ms = kern_ms = 0.0
+    launches = kern_launches = 0
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        model.trainOnBatch(batch)
+        p = ctx.last_profile()
+        dev_ms += p.loop_ms
+        kern_ms += p.iter_kernel_ms
+        kern_launches += p.iter_launches
+        launches += p.iter_launches + p.other_launches
+        kbytes = p.iter_kernel_bytes
+    barrier()
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    clocks = sampler.stop() if rank == 0 else None
+    dev_ms = max_over_ranks(dev_ms)
+    wall_ms = max_over_ranks(wall_ms)
+    kern_ms_per_launch = max_over_ranks(kern_ms / max(kern_launches, 1))
+    assert len(model.lastLossHistory) == iters, "iterations were skipped"
+    value = world * n * iters * args.steps / (dev_ms * 1e-3)
+
+    # ---- end to end through the C ABI with HOST buffers: ingest (H2D) + stats + train + results (D2H)
+    e2e = None
+    if args.workload == "dense_1m" or args.rows:
+        Xh, yh = batch.export_dense()                                   # host copy of this rank's rows
+        Xp = torch.from_numpy(Xh).pin_memory().numpy()
+        del Xh
+        model.setInitialWeights(tw.Vectors.zeros(d))
+
+        def one():
+            b = ctx.batch_from_dense(Xp, yh)
+            st, _, _ = model.step(b, want_arrays=False)
+            w = model.latestModel().weights.toArray()
+            b.free()
+            return st, w
+
+        one()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.e2e_steps):
+            st, w = one()
+        barrier()
+        e2e_s = max_over_ranks(time.perf_counter() - t0)
+        e2e = {"value": world * n * iters * args.e2e_steps / e2e_s, "unit": UNIT,
+               "h2d_bytes_per_step": int(world * n * (d + 1) * 8),
+               "d2h_bytes_per_step": int(world * (d * 8 + iters * 8 + 80)),
+               "steps": args.e2e_steps, "includes": "pinned host -> HBM ingest, stats + %d iterations, weights/loss/stats back" % iters}
+        del Xp
+
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        achieved = kbytes / (kern_ms_per_launch * 1e-3) / 1e9
+        traffic = None
+        try:
+            with open(os.path.join(ROOT, "profiles", "iter_kernel_traffic.json")) as f:
+                t = json.load(f)
+                if t.get("rows") == n and t.get("features") == d:
+                    traffic = t["dram_bytes_per_launch"]
+        except Exception:
+            pass
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f64", "data": "synthetic",
+                "config": {"workload": args.workload, "rows_per_gpu": n, "features": d, "sgd_iterations": iters,
+                           "convergence_tol": 0.0, "parallelism": "rows sharded x%d, NCCL all-gather of shard partials per iteration" % world,
+                           "l2": "inputs (%.1f GB/GPU) larger than L2; no flush needed" % (n * (d + 2) * 8 / 1e9),
+                           "timing": "CUDA events on the library stream around each step's iteration loop, max over ranks"},
+                "wall_ms_per_step": wall_ms / args.steps,
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                             "traffic": traffic, "peak_source": peak_src, "kernel": "k_dense_iter<1,TRAIN>",
+                             "kernel_ms": kern_ms_per_launch, "bytes_per_launch": int(kbytes),
+                             "frac_of_nominal_8TBs": achieved / 8000.0},
+                "clocks": clocks, "e2e": e2e, "gpu_launches": launches}
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"], _, _ = cpu_leg(wl, 3, 1)
+        print(json.dumps(line), flush=True)
+    batch.free()
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

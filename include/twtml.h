@@ -1,0 +1,216 @@
+/*
+ * twtml.h -- C ABI of libtwtml.so: the per-micro-batch learning path of twtml-spark
+ * (QilinGu/twitter-stream-ml) on NVIDIA B200 (sm_100a).
+ *
+ * The reference has no FFI seam on this path: its driver (LinearRegression.scala) calls the
+ * Scala API of org.apache.spark.mllib.regression.StreamingLinearRegressionWithSGD (MLlib
+ * 1.6.1, un-vendored; spark/build.sbt:15) and its own MllibHelper.  Each entry point below
+ * names the reference call site it stands behind; paths are relative to
+ * spark/src/main/scala/com/giorgioinf/twtml/spark/ in the reference tree, "[U]" marks a
+ * class of MLlib 1.6.1.  INTEGRATION.md shows the JNA binding and the Scala facade that keep
+ * those call sites source-compatible.
+ *
+ * Conventions
+ *  - plain C, no C++ types, no exceptions; loadable with JNA / ctypes / dlopen (no jni.h).
+ *  - every function returns 0 (TWTML_OK) or a negative twtml_status; the message of the last
+ *    failure on the calling thread is read with twtml_last_error().
+ *  - every call is blocking: results are on the host when it returns.  Streams are internal.
+ *    A context may be used from any host thread (the Spark JobScheduler does not pin output
+ *    ops to one OS thread), but from one thread at a time per context.
+ *  - the caller owns every pointer it passes; the library copies inputs during the call and
+ *    keeps no caller pointer afterwards.  Opaque handles are released only by their
+ *    _free/_destroy function.
+ *  - there is NO CPU fallback: without an sm_100 device twtml_create fails with TWTML_E_CUDA.
+ *  - all floating point is IEEE binary64 (MLlib vectors are Array[Double]); indices int32,
+ *    row counts / offsets int64.
+ */
+#ifndef TWTML_H
+#define TWTML_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default) /* the library is built with -fvisibility=hidden; only this ABI is exported */
+#endif
+
+#define TWTML_ABI_VERSION 1
+
+typedef enum twtml_status {
+    TWTML_OK = 0,
+    TWTML_E_INVALID_ARG = -1,
+    TWTML_E_NOT_INITIALIZED = -2, /* model used before set_initial_weights: the facade turns this into
+                                     IllegalArgumentException("Model must be initialized before starting
+                                     training." / "... prediction.")  [U] StreamingLinearAlgorithm */
+    TWTML_E_CUDA = -3,
+    TWTML_E_NCCL = -4,
+    TWTML_E_OOM = -5,
+    TWTML_E_SHAPE_MISMATCH = -6,
+    TWTML_E_NONFINITE = -7        /* Utils.round on NaN/Infinity throws NumberFormatException (Utils.scala:4-5) */
+} twtml_status;
+
+typedef struct twtml_ctx twtml_ctx;     /* one GPU (one rank of the row-sharded job) */
+typedef struct twtml_model twtml_model; /* StreamingLinearRegressionWithSGD state: weights + hyper-parameters */
+typedef struct twtml_batch twtml_batch; /* one micro-batch (one RDD[LabeledPoint]) resident in HBM */
+
+/* Numbers the driver loop reports per batch (LinearRegression.scala:59-65, sent on by
+ * SessionStats.scala:22-33).  mse / real_stdev / pred_stdev are rounded with Utils.round like
+ * the reference; the *_raw fields are the same quantities before that last rounding. */
+typedef struct twtml_stats {
+    int64_t batch;         /* rdd.count                                  (:59) */
+    double mse;            /* round(mean((label - round(pred))^2))       (:65) */
+    double real_stdev;     /* round(stdev(label)), population            (:63) */
+    double pred_stdev;     /* round(stdev(round(pred))), population      (:64) */
+    double mse_raw;
+    double real_stdev_raw;
+    double pred_stdev_raw;
+    double real_mean;
+    double pred_mean;
+    int64_t nonfinite;     /* rows whose prediction was NaN/Inf (the reference would throw) */
+} twtml_stats;
+
+/* Device-side timing of the last twtml_train_on_batch / twtml_step on a context, taken with
+ * CUDA events on the library's own stream (measurement aid, no reference counterpart). */
+typedef struct twtml_profile {
+    int32_t iter_launches;   /* fused SGD-iteration kernel launches */
+    int32_t other_launches;  /* reduce / update / stats / cast kernels */
+    int32_t nccl_calls;
+    float iter_kernel_ms;    /* sum of the iteration-kernel durations */
+    float loop_ms;           /* first iteration launch .. last update kernel end */
+    int64_t iter_kernel_bytes; /* algorithmic bytes one iteration-kernel launch reads+writes */
+} twtml_profile;
+
+/* ---- context ------------------------------------------------------------------------------ */
+
+int32_t twtml_abi_version(void);
+
+/* Copies the calling thread's last error message (NUL-terminated, truncated to cap). */
+int32_t twtml_last_error(char* buf, int64_t cap);
+
+/* Single-GPU context on CUDA device `device`.  Stands where the reference creates its
+ * SparkContext (LinearRegression.scala:36): the thing the batches and the model live on. */
+int32_t twtml_create(int32_t device, twtml_ctx** out);
+
+/* One rank of a row-sharded job: world_size processes (or threads), one GPU each, every rank
+ * holding a contiguous block of each micro-batch's rows.  Replaces the executor side of
+ * RDD.treeAggregate + SparkContext.broadcast inside GradientDescent.runMiniBatchSGD [U]: per
+ * iteration the ranks exchange (gradSum[d], lossSum, count) partials with one NCCL all-gather
+ * and add them in a fixed order, so every rank applies the identical update.
+ * nccl_id: TWTML_NCCL_ID_BYTES bytes from twtml_nccl_unique_id() on rank 0, handed to the
+ * other ranks by the host application.  Collective: all ranks must call it together. */
+#define TWTML_NCCL_ID_BYTES 128
+int32_t twtml_nccl_unique_id(uint8_t* out, int64_t cap);
+int32_t twtml_create_ranked(int32_t device, int32_t rank, int32_t world_size, const uint8_t* nccl_id,
+                            int64_t id_bytes, twtml_ctx** out);
+int32_t twtml_destroy(twtml_ctx* ctx);
+int32_t twtml_rank(const twtml_ctx* ctx, int32_t* rank, int32_t* world_size);
+
+int32_t twtml_profile_enable(twtml_ctx* ctx, int32_t on);
+int32_t twtml_profile_get(const twtml_ctx* ctx, twtml_profile* out);
+
+/* ---- model: StreamingLinearRegressionWithSGD [U], built at LinearRegression.scala:28-32 --- */
+
+/* new StreamingLinearRegressionWithSGD(): stepSize 0.1, numIterations 50, miniBatchFraction
+ * 1.0 (class defaults [U]); convergenceTol 0.001, regParam 0.0 (GradientDescent defaults [U]);
+ * weights unset until twtml_set_initial_weights. */
+int32_t twtml_model_create(twtml_ctx* ctx, int64_t num_features, twtml_model** out);
+int32_t twtml_model_free(twtml_model* m);
+int32_t twtml_set_step_size(twtml_model* m, double v);          /* .setStepSize          (:30) */
+int32_t twtml_set_num_iterations(twtml_model* m, int32_t v);    /* .setNumIterations     (:29) */
+int32_t twtml_set_mini_batch_fraction(twtml_model* m, double v);/* .setMiniBatchFraction (:31) */
+int32_t twtml_set_convergence_tol(twtml_model* m, double v);    /* .setConvergenceTol [U] */
+/* regParam and the updater: the reference path uses SimpleUpdater (updater 0), which ignores
+ * regParam [U].  1 = SquaredL2Updater, 2 = L1Updater [U] are offered beyond the reference. */
+int32_t twtml_set_reg_param(twtml_model* m, double v);
+int32_t twtml_set_updater(twtml_model* m, int32_t kind);
+int32_t twtml_set_initial_weights(twtml_model* m, const double* w, int64_t d); /* .setInitialWeights (:32) */
+/* latestModel().weights (:57).  TWTML_E_NOT_INITIALIZED if never set. */
+int32_t twtml_get_weights(const twtml_model* m, double* out, int64_t d);
+int32_t twtml_num_features(const twtml_model* m, int64_t* d);
+
+/* ---- micro-batch ingest --------------------------------------------------------------------- */
+
+/* Raw tweets -> filtered, featurised batch, on the GPU.  Replaces
+ * .filter(MllibHelper.filtrate).map(MllibHelper.featurize) (LinearRegression.scala:44-46;
+ * MllibHelper.scala:42-56,58-71,73-82,84-94) with HashingTF(num_text_features) [U].
+ *  text_utf16/text_off[n+1]: retweetedStatus.getText as UTF-16 code units, ALREADY lower-cased
+ *      by the caller (java String.toLowerCase, MllibHelper.scala:43-45), unless
+ *      TWTML_FLAG_LOWERCASE asks the library to apply the simple one-to-one Unicode BMP
+ *      lower-case map (differs from Java only where Java's mapping is context- or
+ *      length-changing: U+0130, final sigma, and supplementary-plane letters).
+ *  now_ms: System.currentTimeMillis at MllibHelper.scala:61, injected.
+ *  rt_begin/rt_end: numRetweetBegin/End (MllibHelper.scala:15-16), both inclusive.
+ * The batch is CSR of width num_text_features + 4; rows failing the filter are dropped,
+ * order kept.  n may be 0. */
+#define TWTML_FLAG_LOWERCASE 1u
+int32_t twtml_batch_from_tweets(twtml_ctx* ctx, const uint16_t* text_utf16, const int64_t* text_off,
+                                const int32_t* retweet_cnt, const int32_t* followers,
+                                const int32_t* favourites, const int32_t* friends,
+                                const int64_t* created_ms, const uint8_t* is_retweet, int64_t n,
+                                int64_t now_ms, int32_t rt_begin, int32_t rt_end,
+                                int32_t num_text_features, uint32_t flags, twtml_batch** out);
+
+/* An RDD[LabeledPoint] of SparseVectors, packed by the caller (what trainOn receives at
+ * LinearRegression.scala:86).  colidx strictly increasing within a row, < d. */
+int32_t twtml_batch_from_csr(twtml_ctx* ctx, int64_t n, int64_t d, const int64_t* rowptr,
+                             const int32_t* colidx, const double* vals, const double* labels,
+                             twtml_batch** out);
+
+/* The same with DenseVectors: X row-major, row stride ld_x doubles (>= d). */
+int32_t twtml_batch_from_dense(twtml_ctx* ctx, int64_t n, int64_t d, const double* X, int64_t ld_x,
+                               const double* labels, twtml_batch** out);
+
+/* Synthetic micro-batches generated in HBM (measurement tool for SURVEY.md 8d configs 2-5; no
+ * reference counterpart).  Bit-identical to oracle/twtml_oracle.c's generators for the same
+ * (seed, global first row). */
+int32_t twtml_batch_synth_dense(twtml_ctx* ctx, int64_t n, int64_t d, uint64_t seed, int64_t row0,
+                                twtml_batch** out);
+int32_t twtml_batch_synth_csr(twtml_ctx* ctx, int64_t n, int32_t d_text, uint64_t seed, int64_t row0,
+                              twtml_batch** out);
+
+int32_t twtml_batch_rows(const twtml_batch* b, int64_t* n);          /* rdd.count (:59) */
+int32_t twtml_batch_info(const twtml_batch* b, int64_t* n, int64_t* d, int64_t* nnz, int32_t* is_csr);
+/* Copy a CSR batch back (featuriser parity checks).  Buffers sized from twtml_batch_info. */
+int32_t twtml_batch_export_csr(const twtml_batch* b, int64_t* rowptr, int32_t* colidx, double* vals,
+                               double* labels);
+/* Copy a dense batch back: X row-major n x d (ld = d), labels n. */
+int32_t twtml_batch_export_dense(const twtml_batch* b, double* X, double* labels);
+int32_t twtml_batch_free(twtml_batch* b);
+
+/* ---- compute ---------------------------------------------------------------------------------- */
+
+/* predictOnValues / predictOn [U] (mapValues(latestModel.predict)): out_pred[n] = w.x + 0.0,
+ * unrounded, row order kept.  TWTML_E_NOT_INITIALIZED before set_initial_weights. */
+int32_t twtml_predict(const twtml_model* m, const twtml_batch* b, double* out_pred);
+
+/* The stats foreachRDD of the driver loop (LinearRegression.scala:53-66) with the CURRENT
+ * weights: out_real[n] = labels (:61), out_pred_rounded[n] = Utils.round(predict) (:56-58,
+ * :62) -- both nullable -- and the reported numbers.  With ranks, out arrays hold this rank's
+ * rows and *out holds the statistics of the whole batch. */
+int32_t twtml_predict_stats(const twtml_model* m, const twtml_batch* b, double* out_real,
+                            double* out_pred_rounded, twtml_stats* out);
+
+/* One trainOn step (LinearRegression.scala:86 -> StreamingLinearAlgorithm.trainOn ->
+ * GeneralizedLinearAlgorithm.run -> GradientDescent.runMiniBatchSGD [U]) on one micro-batch;
+ * the model's weights are replaced by the result.  An empty batch leaves them untouched.
+ * loss_history[cap] (nullable) receives stochasticLossHistory [U]; *iters_run the iterations
+ * actually executed (convergence can stop early). */
+int32_t twtml_train_on_batch(twtml_model* m, const twtml_batch* b, double* loss_history, int32_t cap,
+                             int32_t* iters_run);
+
+/* Both output ops of one batch interval in reference order -- stats with the pre-training
+ * weights, then training (LinearRegression.scala:53 is registered before :86) -- with the
+ * statistics taken from the tile the first SGD iteration loads, so the batch is read once
+ * less than by the two calls above.  Same results as predict_stats followed by train. */
+int32_t twtml_step(twtml_model* m, const twtml_batch* b, double* out_real, double* out_pred_rounded,
+                   twtml_stats* out, double* loss_history, int32_t cap, int32_t* iters_run);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+#ifdef __cplusplus
+}
+#endif
+#endif /* TWTML_H */

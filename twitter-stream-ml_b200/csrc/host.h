@@ -1,0 +1,100 @@
+// host.h -- host-side structures behind the opaque handles of include/twtml.h.
+#pragma once
+#include <cuda_runtime.h>
+#include <nccl.h> // types only: libnccl is dlopen'ed at run time (nccl_dyn.h), never linked
+
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/twtml.h"
+#include "common.cuh"
+
+namespace twtml {
+
+void set_error(const char* fmt, ...);
+int fail(int code, const char* fmt, ...);
+
+#define TW_CUDA(expr)                                                                                   \
+    do {                                                                                                \
+        cudaError_t e__ = (expr);                                                                       \
+        if (e__ != cudaSuccess)                                                                         \
+            return fail(e__ == cudaErrorMemoryAllocation ? TWTML_E_OOM : TWTML_E_CUDA, "%s: %s (%s:%d)", \
+                        #expr, cudaGetErrorString(e__), __FILE__, __LINE__);                            \
+    } while (0)
+
+#define TW_TRY(expr)            \
+    do {                        \
+        int rc__ = (expr);      \
+        if (rc__ != 0) return rc__; \
+    } while (0)
+
+// a cudaMalloc'ed buffer that only ever grows
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    int reserve(size_t bytes);
+    void release();
+    template <class T> T* as() const { return static_cast<T*>(p); }
+};
+
+} // namespace twtml
+
+struct twtml_ctx {
+    int device = 0, rank = 0, world = 1, sm_count = 148;
+    int spr = twtml::kMaxShards;  // shards per rank
+    int nshards = twtml::kMaxShards;
+    cudaStream_t stream = nullptr;
+    ncclComm_t comm = nullptr;
+    std::mutex mu;
+    // scratch, reused across calls
+    twtml::DevBuf partials, shards, stat_partials, stat_shards, state, loss_hist, out10, tmp_a, tmp_b, gather;
+    // pinned staging ring for host -> device ingest
+    void* pin[2] = {nullptr, nullptr};
+    size_t pin_bytes = 0;
+    cudaEvent_t pin_ev[2] = {nullptr, nullptr};
+    // profiling
+    bool profiling = false;
+    std::vector<cudaEvent_t> ev;
+    twtml_profile prof{};
+};
+
+struct twtml_model {
+    twtml_ctx* ctx = nullptr;
+    int64_t d = 0;
+    double step = 0.1, frac = 1.0, tol = 0.001, reg = 0.0;
+    int num_iter = 50, updater = 0;
+    bool initialized = false;
+    double* d_w = nullptr; // device weights, d rounded up
+    std::vector<double> h_w;
+};
+
+struct twtml_batch {
+    twtml_ctx* ctx = nullptr;
+    bool csr = false;
+    int64_t n = 0, d = 0, nnz = 0;
+    int64_t n_global = 0, row0_global = 0;
+    // dense
+    double* X = nullptr;
+    int64_t ldx = 0;
+    // csr (+ its transpose for the column pass)
+    long long* rowptr = nullptr;
+    int* colidx = nullptr;
+    double* vals = nullptr;
+    double* labels = nullptr;
+    long long* colptr = nullptr;
+    int* rowidx = nullptr;
+    double* cvals = nullptr;
+    twtml::Plan plan{};
+};
+
+namespace twtml {
+// shared between twtml.cu and twtml_sparse.cu
+int upload_plain(twtml_ctx* ctx, void* dst, const void* src, size_t bytes);
+int ctx_global_rows(twtml_ctx* ctx, int64_t n_local, int64_t* n_global, int64_t* row0);
+void make_plan(int64_t n_local, int spr, int R, Plan& p);
+struct Guard {
+    std::lock_guard<std::mutex> lk;
+    explicit Guard(twtml_ctx* c) : lk(c->mu) { cudaSetDevice(c->device); }
+};
+} // namespace twtml

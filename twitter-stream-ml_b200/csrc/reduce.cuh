@@ -1,0 +1,209 @@
+// reduce.cuh -- fixed-order reductions behind the iteration kernels (K4) and the statistics block.
+//
+//   k_shard_reduce   block partials -> one partial vector per shard   (combOp of treeAggregate [U])
+//   [NCCL all-gather of the shard vectors when the job has more than one rank]
+//   k_update         sum the shard vectors in shard order, then SimpleUpdater.compute [U] and
+//                    GradientDescent.isConverged [U]; one CTA, so the order is fixed
+//   k_stats_shard / k_stats_final   Chan merges of the StatCounter tuples in block / shard order,
+//                    then the roundings of LinearRegression.scala:63-65
+#pragma once
+#include "common.cuh"
+
+namespace twtml {
+
+// grid (ceil(pv/32), spr), block (32, 32).  Thread (x, y): column bx*32+x, slice y of the shard's
+// blocks, summed in block order; then the 32 slice sums are added in slice order.
+__global__ void __launch_bounds__(1024) k_shard_reduce(const double* __restrict__ partials, int pv, Plan plan,
+                                                       double* __restrict__ shard_out /* spr x pv */,
+                                                       const TrainState* state)
+{
+    if (state && state->done) return;
+    __shared__ double sm[32][33];
+    const int s = blockIdx.y;
+    const int col = blockIdx.x * 32 + threadIdx.x;
+    const long long b0 = plan.shard_blk0[s], B = plan.shard_blk0[s + 1] - b0;
+    const long long lo = b0 + B * threadIdx.y / 32, hi = b0 + B * (threadIdx.y + 1) / 32;
+    double acc = 0.0;
+    if (col < pv) {
+        long long b = lo;
+        for (; b + 4 <= hi; b += 4) {
+            const double v0 = partials[(b + 0) * pv + col], v1 = partials[(b + 1) * pv + col];
+            const double v2 = partials[(b + 2) * pv + col], v3 = partials[(b + 3) * pv + col];
+            acc += v0;
+            acc += v1;
+            acc += v2;
+            acc += v3;
+        }
+        for (; b < hi; ++b) acc += partials[b * pv + col];
+    }
+    sm[threadIdx.y][threadIdx.x] = acc;
+    __syncthreads();
+    if (threadIdx.y == 0 && col < pv) {
+        double tot = 0.0;
+#pragma unroll
+        for (int q = 0; q < 32; ++q) tot += sm[q][threadIdx.x];
+        shard_out[(long long)s * pv + col] = tot;
+    }
+}
+
+struct UpdateArgs {
+    const double* shards; // nshards x pv   (all ranks' shard vectors, shard order)
+    double* w;            // d
+    TrainState* state;
+    double* loss_hist;    // max_iter
+    int nshards, pv, d, ldx;
+    int max_iter, updater;
+    double step, reg, tol;
+};
+
+__device__ __forceinline__ double block_sum_1024(double v, double* sm32)
+{
+    // fixed tree: butterfly inside each warp, then warp 0 folds the 32 warp sums the same way
+    for (int m = 16; m >= 1; m >>= 1) v += shfl_xor_f64(v, m);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __syncthreads();
+    if (lane == 0) sm32[warp] = v;
+    __syncthreads();
+    double r = sm32[lane];
+    for (int m = 16; m >= 1; m >>= 1) r += shfl_xor_f64(r, m);
+    return r; // identical in every thread
+}
+
+// One CTA of 1024 threads.  Updaters [U] optimization/Updater.scala: 0 Simple (the reference path),
+// 1 SquaredL2, 2 L1.  a*b+c is deliberately NOT fused here (the JVM does not fuse).
+__global__ void __launch_bounds__(1024) k_update(const UpdateArgs a)
+{
+    __shared__ double sm32[32];
+    TrainState* st = a.state;
+    if (st->done) return;
+    const int i = st->iter;
+    double cnt = 0.0, loss = 0.0;
+    for (int s = 0; s < a.nshards; ++s) {
+        loss += a.shards[(long long)s * a.pv + a.ldx];
+        cnt += a.shards[(long long)s * a.pv + a.ldx + 1];
+    }
+    double dn2 = 0.0, wn2 = 0.0, l1 = 0.0;
+    if (cnt > 0.0) {
+        const double this_step = a.step / sqrt((double)i);
+        for (int j = threadIdx.x; j < a.d; j += blockDim.x) {
+            double g = 0.0;
+            for (int s = 0; s < a.nshards; ++s) g += a.shards[(long long)s * a.pv + j];
+            g = g / cnt;
+            const double wo = a.w[j];
+            double wn;
+            if (a.updater == 1) {
+                wn = __dmul_rn(wo, 1.0 - this_step * a.reg);
+                wn = __dadd_rn(wn, __dmul_rn(-this_step, g));
+            } else {
+                wn = __dadd_rn(wo, __dmul_rn(-this_step, g));
+                if (a.updater == 2) {
+                    const double shr = a.reg * this_step;
+                    const double m = fabs(wn) - shr;
+                    const double sg = (double)((wn > 0.0) - (wn < 0.0));
+                    wn = sg * (m > 0.0 ? m : 0.0);
+                }
+            }
+            a.w[j] = wn;
+            const double df = wo - wn;
+            dn2 += df * df;
+            wn2 += wn * wn;
+            l1 += fabs(wn);
+        }
+    }
+    dn2 = block_sum_1024(dn2, sm32);
+    wn2 = block_sum_1024(wn2, sm32);
+    l1 = block_sum_1024(l1, sm32);
+    if (threadIdx.x == 0) {
+        bool converged = false;
+        if (cnt > 0.0) {
+            a.loss_hist[st->nhist] = loss / cnt + st->reg_val;
+            st->nhist += 1;
+            const double wn = sqrt(wn2);
+            st->reg_val = a.updater == 1 ? 0.5 * a.reg * wn * wn : (a.updater == 2 ? l1 * a.reg : 0.0);
+            if (i >= 2) converged = sqrt(dn2) < a.tol * fmax(wn, 1.0);
+        }
+        st->last_count = cnt;
+        st->iter = i + 1;
+        if (converged || i + 1 > a.max_iter) st->done = 1;
+    }
+}
+
+// regVal before the first iteration = updater.compute(w, 0, 0, 1, regParam)._2 [U]
+__global__ void __launch_bounds__(1024) k_train_init(TrainState* st, const double* w, int d, int updater, double reg,
+                                                     int max_iter)
+{
+    __shared__ double sm32[32];
+    double n2 = 0.0, l1 = 0.0;
+    for (int j = threadIdx.x; j < d; j += blockDim.x) { n2 += w[j] * w[j]; l1 += fabs(w[j]); }
+    n2 = block_sum_1024(n2, sm32);
+    l1 = block_sum_1024(l1, sm32);
+    if (threadIdx.x == 0) {
+        st->iter = 1;
+        st->done = max_iter < 1 ? 1 : 0;
+        st->nhist = 0;
+        st->pad = 0;
+        const double nrm = sqrt(n2);
+        st->reg_val = updater == 1 ? 0.5 * reg * nrm * nrm : (updater == 2 ? l1 * reg : 0.0);
+        st->last_count = 0.0;
+    }
+}
+
+// grid spr, block 256: thread t merges slice t of the shard's block tuples in block order, then
+// thread 0 merges the 256 slice tuples in slice order.
+__global__ void __launch_bounds__(256) k_stats_shard(const double* __restrict__ stat_partials, Plan plan,
+                                                     double* __restrict__ shard_out /* spr x kStatStride */)
+{
+    __shared__ double sm[256 * kStatStride];
+    const int s = blockIdx.x, t = threadIdx.x;
+    const long long b0 = plan.shard_blk0[s], B = plan.shard_blk0[s + 1] - b0;
+    const long long lo = b0 + B * t / 256, hi = b0 + B * (t + 1) / 256;
+    Stat7 acc;
+    stat_zero(acc);
+    for (long long b = lo; b < hi; ++b) {
+        Stat7 v;
+        stat_load(v, stat_partials + b * kStatStride);
+        stat_merge(acc, v);
+    }
+    stat_store(sm + t * kStatStride, acc);
+    __syncthreads();
+    if (t == 0) {
+        Stat7 tot;
+        stat_zero(tot);
+        for (int q = 0; q < 256; ++q) {
+            Stat7 v;
+            stat_load(v, sm + q * kStatStride);
+            stat_merge(tot, v);
+        }
+        stat_store(shard_out + (long long)s * kStatStride, tot);
+    }
+}
+
+// out10: batch, mse, real_stdev, pred_stdev (Utils.round applied), mse_raw, real_stdev_raw,
+// pred_stdev_raw, real_mean, pred_mean, nonfinite
+__global__ void k_stats_final(const double* __restrict__ shards, int nshards, double* __restrict__ out10)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    Stat7 tot;
+    stat_zero(tot);
+    for (int s = 0; s < nshards; ++s) {
+        Stat7 v;
+        stat_load(v, shards + (long long)s * kStatStride);
+        stat_merge(tot, v);
+    }
+    const double nan = __longlong_as_double(0x7ff8000000000000ll);
+    const double rs = tot.n > 0.0 ? sqrt(tot.m2_y / tot.n) : nan;
+    const double ps = tot.n > 0.0 ? sqrt(tot.m2_p / tot.n) : nan;
+    const double mse = tot.n > 0.0 ? tot.mu_e : nan;
+    out10[0] = tot.n;
+    out10[1] = round_half_up(mse);
+    out10[2] = round_half_up(rs);
+    out10[3] = round_half_up(ps);
+    out10[4] = mse;
+    out10[5] = rs;
+    out10[6] = ps;
+    out10[7] = tot.mu_y;
+    out10[8] = tot.mu_p;
+    out10[9] = tot.bad;
+}
+
+} // namespace twtml

@@ -1,0 +1,881 @@
+// twtml.cu -- the C ABI of include/twtml.h: contexts, models, dense micro-batches, and the
+// predict / statistics / training entry points.  CSR batches and the tweet featuriser live in
+// twtml_sparse.cu.  Host code here only validates, stages and enqueues: all arithmetic of the
+// learning path runs in the kernels of dense.cuh / reduce.cuh / csr.cuh (no CPU fallback).
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <functional>
+#include <thread>
+
+#include "dense.cuh"
+#include "host.h"
+#include "nccl_dyn.h"
+#include "reduce.cuh"
+#include "synth.cuh"
+
+namespace twtml {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int fail(int code, const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+int DevBuf::reserve(size_t bytes)
+{
+    if (bytes <= cap) return 0;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    size_t want = (bytes + 255) & ~(size_t)255;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e != cudaSuccess) {
+        p = nullptr;
+        return fail(TWTML_E_OOM, "cudaMalloc(%zu): %s", want, cudaGetErrorString(e));
+    }
+    cap = want;
+    return 0;
+}
+
+void DevBuf::release()
+{
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+}
+
+#define TW_NCCL(expr)                                                                                     \
+    do {                                                                                                  \
+        ncclResult_t r__ = (expr);                                                                        \
+        if (r__ != ncclSuccess) return fail(TWTML_E_NCCL, "%s: %s", #expr, nccl_api().GetErrorString(r__)); \
+    } while (0)
+
+// ---------------------------------------------------------------------------------------------
+// plans
+// ---------------------------------------------------------------------------------------------
+struct DenseCfg {
+    int cp, c2, c2p, rl, R, nstages, grid_per_sm;
+    unsigned stage_stride;
+    size_t smem;
+};
+
+static int dense_cfg(int64_t d, DenseCfg& c)
+{
+    const int64_t ldx = (d + 2) & ~(int64_t)1; // round_up(d + 1, 2)
+    const int64_t c2 = ldx / 2;
+    if (c2 <= kIterThreads) c.cp = 1;
+    else if (c2 <= 2 * kIterThreads) c.cp = 2;
+    else if (c2 <= 4 * kIterThreads) c.cp = 4;
+    else return fail(TWTML_E_INVALID_ARG, "dense batches support num_features <= %d; use the CSR form for wider rows", 8 * kIterThreads - 1);
+    c.c2 = (int)c2;
+    if (c.cp == 1) {
+        c.c2p = (c.c2 + 31) & ~31;
+        c.rl = std::min(16, kIterThreads / c.c2p);
+    } else {
+        c.c2p = kIterThreads;
+        c.rl = 1;
+    }
+    c.R = (4 / c.cp) * c.rl;
+    c.stage_stride = (unsigned)(((size_t)c.R * ldx * 8 + 127) & ~(size_t)127);
+    c.grid_per_sm = c.cp == 1 ? 2 : 1;
+    const size_t budget = c.cp == 1 ? (228 * 1024 / 2 - 1024) : 227 * 1024;
+    int s = (int)((budget - IterSmem::kStages) / c.stage_stride);
+    c.nstages = std::min(8, s);
+    if (c.nstages < 2) return fail(TWTML_E_INVALID_ARG, "row too wide for the dense pipeline");
+    c.smem = IterSmem::kStages + (size_t)c.nstages * c.stage_stride;
+    return 0;
+}
+
+void make_plan(int64_t n_local, int spr, int R, Plan& p)
+{
+    memset(&p, 0, sizeof(p));
+    p.spr = spr;
+    const int64_t nominal = (n_local + spr - 1) / spr;
+    int64_t rb = 512;
+    while (rb > 1 && rb * 64 > nominal) rb >>= 1;
+    rb = std::max<int64_t>(1, rb / R) * R;
+    p.rb = (int)rb;
+    long long blk = 0;
+    for (int s = 0; s <= spr; ++s) {
+        p.shard_row0[s] = n_local * s / spr;
+        if (s > 0) {
+            const long long rows = p.shard_row0[s] - p.shard_row0[s - 1];
+            blk += (rows + rb - 1) / rb;
+        }
+        p.shard_blk0[s] = blk;
+    }
+    for (int s = spr + 1; s <= kMaxShards; ++s) { p.shard_row0[s] = n_local; p.shard_blk0[s] = blk; }
+    p.nblocks = blk;
+}
+
+// ---------------------------------------------------------------------------------------------
+// iteration-kernel dispatch
+// ---------------------------------------------------------------------------------------------
+template <int CP, int MODE>
+static int launch_iter_t(twtml_ctx* ctx, const DenseCfg& c, const DenseIterArgs& a)
+{
+    static bool attr_set[16] = {false};
+    auto kern = k_dense_iter<CP, MODE>;
+    if (!attr_set[ctx->device & 15]) {
+        TW_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        attr_set[ctx->device & 15] = true;
+    }
+    long long grid = (long long)ctx->sm_count * c.grid_per_sm;
+    if (grid > a.plan.nblocks) grid = a.plan.nblocks;
+    if (grid < 1) return 0;
+    kern<<<(unsigned)grid, kIterThreads, c.smem, ctx->stream>>>(a);
+    TW_CUDA(cudaGetLastError());
+    return 0;
+}
+
+template <int CP>
+static int launch_iter_cp(twtml_ctx* ctx, const DenseCfg& c, const DenseIterArgs& a, int mode)
+{
+    switch (mode) {
+    case MODE_TRAIN: return launch_iter_t<CP, MODE_TRAIN>(ctx, c, a);
+    case MODE_TRAIN_STATS: return launch_iter_t<CP, MODE_TRAIN_STATS>(ctx, c, a);
+    case MODE_PREDICT: return launch_iter_t<CP, MODE_PREDICT>(ctx, c, a);
+    default: return launch_iter_t<CP, MODE_PREDICT_STATS>(ctx, c, a);
+    }
+}
+
+static int launch_iter(twtml_ctx* ctx, const DenseCfg& c, const DenseIterArgs& a, int mode)
+{
+    if (c.cp == 1) return launch_iter_cp<1>(ctx, c, a, mode);
+    if (c.cp == 2) return launch_iter_cp<2>(ctx, c, a, mode);
+    return launch_iter_cp<4>(ctx, c, a, mode);
+}
+
+// sparse side (twtml_sparse.cu)
+int csr_launch_iter(twtml_ctx* ctx, const twtml_model* m, const twtml_batch* b, int mode, double* out_pred,
+                    double* out_real, int iter_override);
+int csr_partial_width(const twtml_batch* b);
+int csr_reduce(twtml_ctx* ctx, const twtml_batch* b, double* shard_out, const TrainState* gate);
+
+// ---------------------------------------------------------------------------------------------
+// collectives
+// ---------------------------------------------------------------------------------------------
+static int allgather_inplace(twtml_ctx* ctx, void* buf, size_t count_per_rank, ncclDataType_t dt, size_t elem)
+{
+    if (ctx->world == 1) return 0;
+    const char* send = static_cast<const char*>(buf) + (size_t)ctx->rank * count_per_rank * elem;
+    TW_NCCL(nccl_api().AllGather(send, buf, count_per_rank, dt, ctx->comm, ctx->stream));
+    ctx->prof.nccl_calls += 1;
+    return 0;
+}
+
+int ctx_global_rows(twtml_ctx* ctx, int64_t n_local, int64_t* n_global, int64_t* row0)
+{
+    if (ctx->world == 1) { *n_global = n_local; *row0 = 0; return 0; }
+    TW_TRY(ctx->gather.reserve(sizeof(long long) * ctx->world));
+    long long* g = ctx->gather.as<long long>();
+    long long v = n_local;
+    TW_CUDA(cudaMemcpyAsync(g + ctx->rank, &v, sizeof(v), cudaMemcpyHostToDevice, ctx->stream));
+    TW_TRY(allgather_inplace(ctx, g, 1, ncclInt64, sizeof(long long)));
+    std::vector<long long> h(ctx->world);
+    TW_CUDA(cudaMemcpyAsync(h.data(), g, sizeof(long long) * ctx->world, cudaMemcpyDeviceToHost, ctx->stream));
+    TW_CUDA(cudaStreamSynchronize(ctx->stream));
+    long long tot = 0, before = 0;
+    for (int r = 0; r < ctx->world; ++r) { if (r < ctx->rank) before += h[r]; tot += h[r]; }
+    *n_global = tot;
+    *row0 = before;
+    return 0;
+}
+
+static int ensure_pinned(twtml_ctx* ctx, size_t bytes)
+{
+    if (ctx->pin_bytes >= bytes) return 0;
+    for (int i = 0; i < 2; ++i) {
+        if (ctx->pin[i]) cudaFreeHost(ctx->pin[i]);
+        ctx->pin[i] = nullptr;
+    }
+    ctx->pin_bytes = 0;
+    for (int i = 0; i < 2; ++i) TW_CUDA(cudaMallocHost(&ctx->pin[i], bytes));
+    ctx->pin_bytes = bytes;
+    return 0;
+}
+
+// Host -> device in chunks through the two pinned buffers: chunk k+1 is packed by `pack` while chunk
+// k is in flight.  pack(dst, first_unit, n_units) fills dst with n_units * unit_bytes bytes.
+template <class PackFn>
+int staged_upload(twtml_ctx* ctx, void* dst, size_t unit_bytes, int64_t n_units, PackFn pack)
+{
+    if (n_units <= 0) return 0;
+    const size_t chunk_bytes = (size_t)32 << 20;
+    TW_TRY(ensure_pinned(ctx, std::max(chunk_bytes, unit_bytes)));
+    const int64_t per = std::max<int64_t>(1, (int64_t)(ctx->pin_bytes / unit_bytes));
+    int k = 0;
+    for (int64_t u0 = 0; u0 < n_units; u0 += per, ++k) {
+        const int64_t nu = std::min(per, n_units - u0);
+        const int bi = k & 1;
+        if (k >= 2) TW_CUDA(cudaEventSynchronize(ctx->pin_ev[bi]));
+        pack(static_cast<char*>(ctx->pin[bi]), u0, nu);
+        TW_CUDA(cudaMemcpyAsync(static_cast<char*>(dst) + (size_t)u0 * unit_bytes, ctx->pin[bi], (size_t)nu * unit_bytes,
+                                cudaMemcpyHostToDevice, ctx->stream));
+        TW_CUDA(cudaEventRecord(ctx->pin_ev[bi], ctx->stream));
+    }
+    return 0;
+}
+int upload_plain(twtml_ctx* ctx, void* dst, const void* src, size_t bytes)
+{
+    const char* s = static_cast<const char*>(src);
+    return staged_upload(ctx, dst, 1, (int64_t)bytes, [s](char* out, int64_t u0, int64_t nu) { memcpy(out, s + u0, (size_t)nu); });
+}
+
+static void parallel_rows(int64_t n, int64_t min_per_thread, const std::function<void(int64_t, int64_t)>& fn)
+{
+    int hw = (int)std::thread::hardware_concurrency();
+    int nt = (int)std::min<int64_t>(std::max(1, std::min(hw, 16)), std::max<int64_t>(1, n / min_per_thread));
+    if (nt <= 1) { fn(0, n); return; }
+    std::vector<std::thread> th;
+    for (int i = 0; i < nt; ++i) th.emplace_back(fn, n * i / nt, n * (i + 1) / nt);
+    for (auto& t : th) t.join();
+}
+
+__global__ void k_scatter_labels(double* __restrict__ X, long long ldx, int d, const double* __restrict__ labels, long long n)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    X[i * ldx + d] = labels[i];
+    for (long long j = d + 1; j < ldx; ++j) X[i * ldx + j] = 0.0;
+}
+
+__global__ void k_gather_dense(const double* __restrict__ X, long long ldx, int d, double* __restrict__ out,
+                               double* __restrict__ labels, long long n)
+{
+    for (long long i = blockIdx.x; i < n; i += gridDim.x) {
+        for (int j = threadIdx.x; j < d; j += blockDim.x) out[i * d + j] = X[i * ldx + j];
+        if (threadIdx.x == 0) labels[i] = X[i * ldx + d];
+    }
+}
+
+static void stats_from_out10(const double* o, twtml_stats* s)
+{
+    s->batch = (int64_t)o[0];
+    s->mse = o[1];
+    s->real_stdev = o[2];
+    s->pred_stdev = o[3];
+    s->mse_raw = o[4];
+    s->real_stdev_raw = o[5];
+    s->pred_stdev_raw = o[6];
+    s->real_mean = o[7];
+    s->pred_mean = o[8];
+    s->nonfinite = (int64_t)o[9];
+}
+
+static void stats_empty(twtml_stats* s)
+{
+    memset(s, 0, sizeof(*s));
+    s->mse = s->real_stdev = s->pred_stdev = s->mse_raw = s->real_stdev_raw = s->pred_stdev_raw = s->real_mean = s->pred_mean = NAN;
+}
+
+static cudaEvent_t prof_event(twtml_ctx* ctx, size_t i)
+{
+    while (ctx->ev.size() <= i) {
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        ctx->ev.push_back(e);
+    }
+    return ctx->ev[i];
+}
+
+// One pass of the iteration kernel in `mode` over batch b (dense or CSR).
+static int run_pass(twtml_ctx* ctx, const twtml_model* m, const twtml_batch* b, int mode, double* out_pred, double* out_real,
+                    int iter_override)
+{
+    if (b->csr) return csr_launch_iter(ctx, m, b, mode, out_pred, out_real, iter_override);
+    DenseCfg c;
+    TW_TRY(dense_cfg(b->d, c));
+    DenseIterArgs a{};
+    a.X = b->X;
+    a.w = m->d_w;
+    a.state = ctx->state.as<TrainState>();
+    a.partials = ctx->partials.as<double>();
+    a.stat_partials = ctx->stat_partials.as<double>();
+    a.out_pred = out_pred;
+    a.out_real = out_real;
+    a.plan = b->plan;
+    a.ldx = b->ldx;
+    a.d = (int)b->d;
+    a.c2 = c.c2;
+    a.c2p = c.c2p;
+    a.rl = c.rl;
+    a.nstages = c.nstages;
+    a.stage_stride = c.stage_stride;
+    a.frac = m->frac;
+    a.row0_global = (unsigned long long)b->row0_global;
+    a.iter_override = iter_override;
+    return launch_iter(ctx, c, a, mode);
+}
+
+static int partial_width(const twtml_batch* b) { return b->csr ? csr_partial_width(b) : (int)b->ldx + 2; }
+static int loss_slot(const twtml_batch* b) { return b->csr ? (int)b->d : (int)b->ldx; }
+
+static int reserve_scratch(twtml_ctx* ctx, const twtml_model* m, const twtml_batch* b)
+{
+    const int pv = partial_width(b);
+    TW_TRY(ctx->partials.reserve(sizeof(double) * (size_t)std::max<long long>(1, b->plan.nblocks) * pv));
+    TW_TRY(ctx->shards.reserve(sizeof(double) * (size_t)kMaxShards * std::max(1, ctx->world) * pv));
+    TW_TRY(ctx->stat_partials.reserve(sizeof(double) * (size_t)std::max<long long>(1, b->plan.nblocks) * kStatStride));
+    TW_TRY(ctx->stat_shards.reserve(sizeof(double) * (size_t)kMaxShards * std::max(1, ctx->world) * kStatStride));
+    TW_TRY(ctx->state.reserve(sizeof(TrainState)));
+    TW_TRY(ctx->loss_hist.reserve(sizeof(double) * (size_t)std::max(1, m->num_iter)));
+    TW_TRY(ctx->out10.reserve(sizeof(double) * 16));
+    return 0;
+}
+
+// block partials -> shard vectors -> (all-gather) ; leaves every rank with all shard vectors
+static int reduce_partials(twtml_ctx* ctx, const twtml_batch* b, bool gated)
+{
+    const int pv = partial_width(b), spr = b->plan.spr;
+    const TrainState* gate = gated ? ctx->state.as<TrainState>() : nullptr;
+    double* mine = ctx->shards.as<double>() + (size_t)ctx->rank * spr * pv;
+    if (b->csr) {
+        TW_TRY(csr_reduce(ctx, b, mine, gate));
+    } else {
+        dim3 grid((pv + 31) / 32, spr), block(32, 32);
+        k_shard_reduce<<<grid, block, 0, ctx->stream>>>(ctx->partials.as<double>(), pv, b->plan, mine, gate);
+        TW_CUDA(cudaGetLastError());
+        ctx->prof.other_launches += 1;
+    }
+    return allgather_inplace(ctx, ctx->shards.as<double>(), (size_t)spr * pv, ncclDouble, sizeof(double));
+}
+
+static int reduce_stats(twtml_ctx* ctx, const twtml_batch* b)
+{
+    const int spr = b->plan.spr;
+    double* mine = ctx->stat_shards.as<double>() + (size_t)ctx->rank * spr * kStatStride;
+    k_stats_shard<<<spr, 256, 0, ctx->stream>>>(ctx->stat_partials.as<double>(), b->plan, mine);
+    TW_CUDA(cudaGetLastError());
+    TW_TRY(allgather_inplace(ctx, ctx->stat_shards.as<double>(), (size_t)spr * kStatStride, ncclDouble, sizeof(double)));
+    k_stats_final<<<1, 32, 0, ctx->stream>>>(ctx->stat_shards.as<double>(), spr * ctx->world, ctx->out10.as<double>());
+    TW_CUDA(cudaGetLastError());
+    ctx->prof.other_launches += 2;
+    return 0;
+}
+
+static int check_pair(const twtml_model* m, const twtml_batch* b, const char* what)
+{
+    if (!m || !b) return fail(TWTML_E_INVALID_ARG, "%s: null handle", what);
+    if (m->ctx != b->ctx) return fail(TWTML_E_INVALID_ARG, "%s: model and batch belong to different contexts", what);
+    if (!m->initialized)
+        return fail(TWTML_E_NOT_INITIALIZED, "Model must be initialized before starting %s.", what);
+    if (m->d != b->d)
+        return fail(TWTML_E_SHAPE_MISMATCH, "%s: model has %lld features, batch has %lld", what, (long long)m->d, (long long)b->d);
+    return 0;
+}
+
+static int fetch_rows(twtml_ctx* ctx, double* host, const double* dev, int64_t n)
+{
+    if (host && n > 0) TW_CUDA(cudaMemcpyAsync(host, dev, sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+    return 0;
+}
+
+static int do_predict_stats(const twtml_model* m, const twtml_batch* b, double* out_real, double* out_pred, twtml_stats* out)
+{
+    twtml_ctx* ctx = m->ctx;
+    if (b->n_global == 0) { stats_empty(out); return 0; }
+    TW_TRY(reserve_scratch(ctx, m, b));
+    double *dp = nullptr, *dr = nullptr;
+    if (out_pred) { TW_TRY(ctx->tmp_a.reserve(sizeof(double) * (size_t)std::max<int64_t>(1, b->n))); dp = ctx->tmp_a.as<double>(); }
+    if (out_real) { TW_TRY(ctx->tmp_b.reserve(sizeof(double) * (size_t)std::max<int64_t>(1, b->n))); dr = ctx->tmp_b.as<double>(); }
+    TW_TRY(run_pass(ctx, m, b, MODE_PREDICT_STATS, dp, dr, 0));
+    TW_TRY(reduce_stats(ctx, b));
+    double o[10];
+    TW_CUDA(cudaMemcpyAsync(o, ctx->out10.p, sizeof(o), cudaMemcpyDeviceToHost, ctx->stream));
+    TW_TRY(fetch_rows(ctx, out_pred, dp, b->n));
+    TW_TRY(fetch_rows(ctx, out_real, dr, b->n));
+    TW_CUDA(cudaStreamSynchronize(ctx->stream));
+    stats_from_out10(o, out);
+    return 0;
+}
+
+static int do_train(twtml_model* m, const twtml_batch* b, bool with_stats, double* out_real, double* out_pred, twtml_stats* out,
+                    double* loss_history, int32_t cap, int32_t* iters_run)
+{
+    twtml_ctx* ctx = m->ctx;
+    if (iters_run) *iters_run = 0;
+    ctx->prof = twtml_profile{};
+    if (b->n_global == 0) { // rdd.isEmpty: both output ops skip the batch
+        if (with_stats && out) stats_empty(out);
+        return 0;
+    }
+    TW_TRY(reserve_scratch(ctx, m, b));
+    double *dp = nullptr, *dr = nullptr;
+    if (with_stats && out_pred) { TW_TRY(ctx->tmp_a.reserve(sizeof(double) * (size_t)std::max<int64_t>(1, b->n))); dp = ctx->tmp_a.as<double>(); }
+    if (with_stats && out_real) { TW_TRY(ctx->tmp_b.reserve(sizeof(double) * (size_t)std::max<int64_t>(1, b->n))); dr = ctx->tmp_b.as<double>(); }
+
+    TrainState* st = ctx->state.as<TrainState>();
+    k_train_init<<<1, 1024, 0, ctx->stream>>>(st, m->d_w, (int)m->d, m->updater, m->reg, m->num_iter);
+    TW_CUDA(cudaGetLastError());
+    if (with_stats && m->num_iter < 1) { // no iteration to ride on
+        TW_TRY(run_pass(ctx, m, b, MODE_PREDICT_STATS, dp, dr, 0));
+        TW_TRY(reduce_stats(ctx, b));
+    }
+    const int pv = partial_width(b);
+    UpdateArgs ua{};
+    ua.shards = ctx->shards.as<double>();
+    ua.w = m->d_w;
+    ua.state = st;
+    ua.loss_hist = ctx->loss_hist.as<double>();
+    ua.nshards = b->plan.spr * ctx->world;
+    ua.pv = pv;
+    ua.d = (int)m->d;
+    ua.ldx = loss_slot(b);
+    ua.max_iter = m->num_iter;
+    ua.updater = m->updater;
+    ua.step = m->step;
+    ua.reg = m->reg;
+    ua.tol = m->tol;
+
+    const bool prof = ctx->profiling;
+    size_t ne = 0;
+    if (prof) TW_CUDA(cudaEventRecord(prof_event(ctx, ne++), ctx->stream));
+    for (int i = 1; i <= m->num_iter; ++i) {
+        const int mode = (i == 1 && with_stats) ? MODE_TRAIN_STATS : MODE_TRAIN;
+        if (prof) TW_CUDA(cudaEventRecord(prof_event(ctx, ne++), ctx->stream));
+        TW_TRY(run_pass(ctx, m, b, mode, dp, dr, 0));
+        if (prof) TW_CUDA(cudaEventRecord(prof_event(ctx, ne++), ctx->stream));
+        ctx->prof.iter_launches += 1;
+        TW_TRY(reduce_partials(ctx, b, true));
+        k_update<<<1, 1024, 0, ctx->stream>>>(ua);
+        TW_CUDA(cudaGetLastError());
+        ctx->prof.other_launches += 1;
+        if (i == 1 && with_stats) TW_TRY(reduce_stats(ctx, b));
+    }
+    if (prof) TW_CUDA(cudaEventRecord(prof_event(ctx, ne++), ctx->stream));
+
+    TrainState hs{};
+    double o[10];
+    std::vector<double> hist((size_t)std::max(1, m->num_iter));
+    TW_CUDA(cudaMemcpyAsync(&hs, st, sizeof(hs), cudaMemcpyDeviceToHost, ctx->stream));
+    TW_CUDA(cudaMemcpyAsync(hist.data(), ctx->loss_hist.p, sizeof(double) * hist.size(), cudaMemcpyDeviceToHost, ctx->stream));
+    TW_CUDA(cudaMemcpyAsync(m->h_w.data(), m->d_w, sizeof(double) * (size_t)m->d, cudaMemcpyDeviceToHost, ctx->stream));
+    if (with_stats) {
+        TW_CUDA(cudaMemcpyAsync(o, ctx->out10.p, sizeof(o), cudaMemcpyDeviceToHost, ctx->stream));
+        TW_TRY(fetch_rows(ctx, out_pred, dp, b->n));
+        TW_TRY(fetch_rows(ctx, out_real, dr, b->n));
+    }
+    TW_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (with_stats && out) stats_from_out10(o, out);
+    if (iters_run) *iters_run = hs.nhist;
+    if (loss_history)
+        for (int i = 0; i < hs.nhist && i < cap; ++i) loss_history[i] = hist[i];
+    if (prof) {
+        float ms = 0.f, tot = 0.f;
+        for (int i = 0; i < m->num_iter; ++i) {
+            cudaEventElapsedTime(&ms, ctx->ev[1 + 2 * i], ctx->ev[2 + 2 * i]);
+            tot += ms;
+        }
+        ctx->prof.iter_kernel_ms = tot;
+        cudaEventElapsedTime(&ctx->prof.loop_ms, ctx->ev[0], ctx->ev[ne - 1]);
+        if (b->csr) ctx->prof.iter_kernel_bytes = b->n * 16 + b->nnz * 12 + 16 * b->d;
+        else ctx->prof.iter_kernel_bytes = 8 * b->n * (b->d + 1) + 16 * b->d;
+    }
+    return 0;
+}
+
+} // namespace twtml
+
+using namespace twtml;
+
+// =============================================================================================
+// C ABI
+// =============================================================================================
+extern "C" {
+
+int32_t twtml_abi_version(void) { return TWTML_ABI_VERSION; }
+
+int32_t twtml_last_error(char* buf, int64_t cap)
+{
+    if (!buf || cap <= 0) return TWTML_E_INVALID_ARG;
+    snprintf(buf, (size_t)cap, "%s", g_err);
+    return 0;
+}
+
+static int32_t create_common(int32_t device, int32_t rank, int32_t world, const uint8_t* id, twtml_ctx** out)
+{
+    if (!out) return fail(TWTML_E_INVALID_ARG, "twtml_create: out is null");
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(TWTML_E_CUDA, "no CUDA device (%s); libtwtml has no CPU fallback", e == cudaSuccess ? "count is 0" : cudaGetErrorString(e));
+    if (device < 0 || device >= ndev) return fail(TWTML_E_INVALID_ARG, "device %d out of range [0,%d)", device, ndev);
+    cudaDeviceProp prop;
+    TW_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10)
+        return fail(TWTML_E_CUDA, "device %d is sm_%d%d; libtwtml is built for sm_100a only", device, prop.major, prop.minor);
+    TW_CUDA(cudaSetDevice(device));
+    twtml_ctx* c = new twtml_ctx();
+    c->device = device;
+    c->rank = rank;
+    c->world = world;
+    c->sm_count = prop.multiProcessorCount;
+    // 8 virtual shards in total when the rank count divides 8, so that 1/2/4/8 GPUs add the same
+    // shard vectors in the same order; otherwise one shard per rank.
+    c->spr = (world <= kMaxShards && kMaxShards % world == 0) ? kMaxShards / world : 1;
+    c->nshards = c->spr * world;
+    cudaError_t se = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+    if (se != cudaSuccess) { delete c; return fail(TWTML_E_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(se)); }
+    for (int i = 0; i < 2; ++i) cudaEventCreateWithFlags(&c->pin_ev[i], cudaEventDisableTiming);
+    if (world > 1) {
+        if (!nccl_api().ok) { delete c; return fail(TWTML_E_NCCL, "libnccl.so.2 could not be loaded: %s", dlerror()); }
+        ncclUniqueId uid;
+        memcpy(&uid, id, sizeof(uid));
+        ncclResult_t r = nccl_api().CommInitRank(&c->comm, world, uid, rank);
+        if (r != ncclSuccess) { delete c; return fail(TWTML_E_NCCL, "ncclCommInitRank: %s", nccl_api().GetErrorString(r)); }
+    }
+    *out = c;
+    return 0;
+}
+
+int32_t twtml_create(int32_t device, twtml_ctx** out) { return create_common(device, 0, 1, nullptr, out); }
+
+int32_t twtml_nccl_unique_id(uint8_t* out, int64_t cap)
+{
+    static_assert(sizeof(ncclUniqueId) == TWTML_NCCL_ID_BYTES, "ncclUniqueId size");
+    if (!out || cap < TWTML_NCCL_ID_BYTES) return fail(TWTML_E_INVALID_ARG, "twtml_nccl_unique_id: need %d bytes", TWTML_NCCL_ID_BYTES);
+    if (!nccl_api().ok) return fail(TWTML_E_NCCL, "libnccl.so.2 could not be loaded");
+    ncclUniqueId uid;
+    TW_NCCL(nccl_api().GetUniqueId(&uid));
+    memcpy(out, &uid, sizeof(uid));
+    return 0;
+}
+
+int32_t twtml_create_ranked(int32_t device, int32_t rank, int32_t world_size, const uint8_t* nccl_id, int64_t id_bytes, twtml_ctx** out)
+{
+    if (world_size < 1 || rank < 0 || rank >= world_size) return fail(TWTML_E_INVALID_ARG, "bad rank %d / world %d", rank, world_size);
+    if (world_size > 1 && (!nccl_id || id_bytes < TWTML_NCCL_ID_BYTES)) return fail(TWTML_E_INVALID_ARG, "nccl_id must hold %d bytes", TWTML_NCCL_ID_BYTES);
+    return create_common(device, rank, world_size, nccl_id, out);
+}
+
+int32_t twtml_destroy(twtml_ctx* ctx)
+{
+    if (!ctx) return 0;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    if (ctx->comm) nccl_api().CommDestroy(ctx->comm);
+    for (DevBuf* b : {&ctx->partials, &ctx->shards, &ctx->stat_partials, &ctx->stat_shards, &ctx->state, &ctx->loss_hist, &ctx->out10,
+                      &ctx->tmp_a, &ctx->tmp_b, &ctx->gather})
+        b->release();
+    for (int i = 0; i < 2; ++i) {
+        if (ctx->pin[i]) cudaFreeHost(ctx->pin[i]);
+        if (ctx->pin_ev[i]) cudaEventDestroy(ctx->pin_ev[i]);
+    }
+    for (cudaEvent_t e : ctx->ev) cudaEventDestroy(e);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return 0;
+}
+
+int32_t twtml_rank(const twtml_ctx* ctx, int32_t* rank, int32_t* world_size)
+{
+    if (!ctx) return fail(TWTML_E_INVALID_ARG, "null context");
+    if (rank) *rank = ctx->rank;
+    if (world_size) *world_size = ctx->world;
+    return 0;
+}
+
+int32_t twtml_profile_enable(twtml_ctx* ctx, int32_t on)
+{
+    if (!ctx) return fail(TWTML_E_INVALID_ARG, "null context");
+    ctx->profiling = on != 0;
+    return 0;
+}
+
+int32_t twtml_profile_get(const twtml_ctx* ctx, twtml_profile* out)
+{
+    if (!ctx || !out) return fail(TWTML_E_INVALID_ARG, "null argument");
+    *out = ctx->prof;
+    return 0;
+}
+
+// ---- model ----------------------------------------------------------------------------------
+int32_t twtml_model_create(twtml_ctx* ctx, int64_t num_features, twtml_model** out)
+{
+    if (!ctx || !out) return fail(TWTML_E_INVALID_ARG, "null argument");
+    if (num_features < 1 || num_features > (int64_t)1 << 30) return fail(TWTML_E_INVALID_ARG, "num_features %lld out of range", (long long)num_features);
+    Guard g(ctx);
+    twtml_model* m = new twtml_model();
+    m->ctx = ctx;
+    m->d = num_features;
+    m->h_w.assign((size_t)num_features, 0.0);
+    cudaError_t e = cudaMalloc(&m->d_w, sizeof(double) * (size_t)(num_features + 2));
+    if (e != cudaSuccess) { delete m; return fail(TWTML_E_OOM, "cudaMalloc weights: %s", cudaGetErrorString(e)); }
+    *out = m;
+    return 0;
+}
+
+int32_t twtml_model_free(twtml_model* m)
+{
+    if (!m) return 0;
+    {
+        Guard g(m->ctx);
+        cudaStreamSynchronize(m->ctx->stream);
+        cudaFree(m->d_w);
+    }
+    delete m;
+    return 0;
+}
+
+int32_t twtml_set_step_size(twtml_model* m, double v)
+{
+    if (!m) return fail(TWTML_E_INVALID_ARG, "null model");
+    m->step = v;
+    return 0;
+}
+int32_t twtml_set_num_iterations(twtml_model* m, int32_t v)
+{
+    if (!m) return fail(TWTML_E_INVALID_ARG, "null model");
+    if (v < 0) return fail(TWTML_E_INVALID_ARG, "numIterations must be >= 0");
+    m->num_iter = v;
+    return 0;
+}
+int32_t twtml_set_mini_batch_fraction(twtml_model* m, double v)
+{
+    if (!m) return fail(TWTML_E_INVALID_ARG, "null model");
+    m->frac = v;
+    return 0;
+}
+int32_t twtml_set_convergence_tol(twtml_model* m, double v)
+{
+    if (!m) return fail(TWTML_E_INVALID_ARG, "null model");
+    if (!(v >= 0.0 && v <= 1.0)) return fail(TWTML_E_INVALID_ARG, "convergenceTol must be in [0, 1]"); // require() in GradientDescent [U]
+    m->tol = v;
+    return 0;
+}
+int32_t twtml_set_reg_param(twtml_model* m, double v)
+{
+    if (!m) return fail(TWTML_E_INVALID_ARG, "null model");
+    m->reg = v;
+    return 0;
+}
+int32_t twtml_set_updater(twtml_model* m, int32_t kind)
+{
+    if (!m) return fail(TWTML_E_INVALID_ARG, "null model");
+    if (kind < 0 || kind > 2) return fail(TWTML_E_INVALID_ARG, "updater must be 0 (Simple), 1 (SquaredL2) or 2 (L1)");
+    m->updater = kind;
+    return 0;
+}
+
+int32_t twtml_set_initial_weights(twtml_model* m, const double* w, int64_t d)
+{
+    if (!m || !w) return fail(TWTML_E_INVALID_ARG, "null argument");
+    if (d != m->d) return fail(TWTML_E_SHAPE_MISMATCH, "setInitialWeights: got %lld values for %lld features", (long long)d, (long long)m->d);
+    Guard g(m->ctx);
+    memcpy(m->h_w.data(), w, sizeof(double) * (size_t)d);
+    TW_CUDA(cudaMemcpyAsync(m->d_w, m->h_w.data(), sizeof(double) * (size_t)d, cudaMemcpyHostToDevice, m->ctx->stream));
+    TW_CUDA(cudaStreamSynchronize(m->ctx->stream));
+    m->initialized = true;
+    return 0;
+}
+
+int32_t twtml_get_weights(const twtml_model* m, double* out, int64_t d)
+{
+    if (!m || !out) return fail(TWTML_E_INVALID_ARG, "null argument");
+    if (!m->initialized) return fail(TWTML_E_NOT_INITIALIZED, "Model must be initialized before starting prediction.");
+    if (d != m->d) return fail(TWTML_E_SHAPE_MISMATCH, "get_weights: buffer of %lld for %lld features", (long long)d, (long long)m->d);
+    memcpy(out, m->h_w.data(), sizeof(double) * (size_t)d);
+    return 0;
+}
+
+int32_t twtml_num_features(const twtml_model* m, int64_t* d)
+{
+    if (!m || !d) return fail(TWTML_E_INVALID_ARG, "null argument");
+    *d = m->d;
+    return 0;
+}
+
+// ---- dense batches --------------------------------------------------------------------------
+static int32_t new_dense(twtml_ctx* ctx, int64_t n, int64_t d, twtml_batch** out)
+{
+    DenseCfg c;
+    TW_TRY(dense_cfg(d, c));
+    twtml_batch* b = new twtml_batch();
+    b->ctx = ctx;
+    b->n = n;
+    b->d = d;
+    b->ldx = (d + 2) & ~(int64_t)1;
+    make_plan(n, ctx->spr, c.R, b->plan);
+    if (n > 0) {
+        cudaError_t e = cudaMalloc(&b->X, sizeof(double) * (size_t)n * (size_t)b->ldx);
+        if (e != cudaSuccess) { delete b; return fail(TWTML_E_OOM, "cudaMalloc(%lld x %lld doubles): %s", (long long)n, (long long)b->ldx, cudaGetErrorString(e)); }
+    }
+    int rc = ctx_global_rows(ctx, n, &b->n_global, &b->row0_global);
+    if (rc) { cudaFree(b->X); delete b; return rc; }
+    *out = b;
+    return 0;
+}
+
+int32_t twtml_batch_from_dense(twtml_ctx* ctx, int64_t n, int64_t d, const double* X, int64_t ld_x, const double* labels, twtml_batch** out)
+{
+    if (!ctx || !out) return fail(TWTML_E_INVALID_ARG, "null argument");
+    if (n < 0 || d < 1 || (n > 0 && (!X || !labels)) || ld_x < d) return fail(TWTML_E_INVALID_ARG, "twtml_batch_from_dense: bad shape or null data");
+    Guard g(ctx);
+    twtml_batch* b = nullptr;
+    TW_TRY(new_dense(ctx, n, d, &b));
+    if (n > 0) {
+        const int64_t ldx = b->ldx;
+        cudaPointerAttributes pa{};
+        const bool pinned = cudaPointerGetAttributes(&pa, X) == cudaSuccess && pa.type == cudaMemoryTypeHost;
+        cudaGetLastError();
+        int rc = 0;
+        if (pinned) { // page-locked caller memory: strided DMA straight from it, labels scattered on the device
+            cudaError_t e = cudaMemcpy2DAsync(b->X, (size_t)ldx * 8, X, (size_t)ld_x * 8, (size_t)d * 8, (size_t)n, cudaMemcpyHostToDevice, ctx->stream);
+            if (e != cudaSuccess) rc = fail(TWTML_E_CUDA, "cudaMemcpy2DAsync: %s", cudaGetErrorString(e));
+            if (!rc) rc = ctx->tmp_a.reserve(sizeof(double) * (size_t)n);
+            if (!rc) rc = upload_plain(ctx, ctx->tmp_a.p, labels, sizeof(double) * (size_t)n);
+            if (!rc) {
+                k_scatter_labels<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(b->X, ldx, (int)d, ctx->tmp_a.as<double>(), n);
+                if (cudaGetLastError() != cudaSuccess) rc = fail(TWTML_E_CUDA, "k_scatter_labels launch failed");
+            }
+        } else { // pageable: pack rows [x.., label, pad] into the pinned ring, chunk k+1 while chunk k copies
+            rc = staged_upload(ctx, b->X, (size_t)ldx * 8, n, [&](char* dst, int64_t r0, int64_t nr) {
+                parallel_rows(nr, 2048, [&](int64_t lo, int64_t hi) {
+                    for (int64_t r = lo; r < hi; ++r) {
+                        double* row = reinterpret_cast<double*>(dst) + r * ldx;
+                        memcpy(row, X + (r0 + r) * ld_x, sizeof(double) * (size_t)d);
+                        row[d] = labels[r0 + r];
+                        for (int64_t j = d + 1; j < ldx; ++j) row[j] = 0.0;
+                    }
+                });
+            });
+        }
+        if (!rc && cudaStreamSynchronize(ctx->stream) != cudaSuccess) rc = fail(TWTML_E_CUDA, "upload failed: %s", cudaGetErrorString(cudaGetLastError()));
+        if (rc) { cudaFree(b->X); delete b; return rc; }
+    }
+    *out = b;
+    return 0;
+}
+
+int32_t twtml_batch_synth_dense(twtml_ctx* ctx, int64_t n, int64_t d, uint64_t seed, int64_t row0, twtml_batch** out)
+{
+    if (!ctx || !out) return fail(TWTML_E_INVALID_ARG, "null argument");
+    if (n < 0 || d < 1) return fail(TWTML_E_INVALID_ARG, "twtml_batch_synth_dense: bad shape");
+    Guard g(ctx);
+    twtml_batch* b = nullptr;
+    TW_TRY(new_dense(ctx, n, d, &b));
+    if (n > 0) {
+        const double inv = 1.0 / std::sqrt((double)d);
+        const unsigned gx = (unsigned)std::min<int64_t>(n, (int64_t)ctx->sm_count * 64);
+        k_synth_dense_x<<<gx, 256, 0, ctx->stream>>>(b->X, b->ldx, (int)d, seed, row0, inv, n);
+        k_synth_dense_y<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(b->X, b->ldx, (int)d, seed, row0, inv, n);
+        cudaError_t e = cudaGetLastError();
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        if (e != cudaSuccess) { cudaFree(b->X); delete b; return fail(TWTML_E_CUDA, "synthetic generator: %s", cudaGetErrorString(e)); }
+    }
+    *out = b;
+    return 0;
+}
+
+int32_t twtml_batch_rows(const twtml_batch* b, int64_t* n)
+{
+    if (!b || !n) return fail(TWTML_E_INVALID_ARG, "null argument");
+    *n = b->n;
+    return 0;
+}
+
+int32_t twtml_batch_info(const twtml_batch* b, int64_t* n, int64_t* d, int64_t* nnz, int32_t* is_csr)
+{
+    if (!b) return fail(TWTML_E_INVALID_ARG, "null batch");
+    if (n) *n = b->n;
+    if (d) *d = b->d;
+    if (nnz) *nnz = b->csr ? b->nnz : b->n * b->d;
+    if (is_csr) *is_csr = b->csr ? 1 : 0;
+    return 0;
+}
+
+int32_t twtml_batch_export_dense(const twtml_batch* b, double* X, double* labels)
+{
+    if (!b || !X || !labels) return fail(TWTML_E_INVALID_ARG, "null argument");
+    if (b->csr) return fail(TWTML_E_INVALID_ARG, "twtml_batch_export_dense on a CSR batch");
+    if (b->n == 0) return 0;
+    twtml_ctx* ctx = b->ctx;
+    Guard g(ctx);
+    TW_TRY(ctx->tmp_a.reserve(sizeof(double) * (size_t)b->n * (size_t)b->d));
+    TW_TRY(ctx->tmp_b.reserve(sizeof(double) * (size_t)b->n));
+    k_gather_dense<<<(unsigned)std::min<int64_t>(b->n, 65535), 256, 0, ctx->stream>>>(b->X, b->ldx, (int)b->d, ctx->tmp_a.as<double>(), ctx->tmp_b.as<double>(), b->n);
+    TW_CUDA(cudaGetLastError());
+    TW_CUDA(cudaMemcpyAsync(X, ctx->tmp_a.p, sizeof(double) * (size_t)b->n * (size_t)b->d, cudaMemcpyDeviceToHost, ctx->stream));
+    TW_CUDA(cudaMemcpyAsync(labels, ctx->tmp_b.p, sizeof(double) * (size_t)b->n, cudaMemcpyDeviceToHost, ctx->stream));
+    TW_CUDA(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int32_t twtml_batch_free(twtml_batch* b)
+{
+    if (!b) return 0;
+    {
+        Guard g(b->ctx);
+        cudaStreamSynchronize(b->ctx->stream);
+        cudaFree(b->X);
+        cudaFree(b->rowptr);
+        cudaFree(b->colidx);
+        cudaFree(b->vals);
+        cudaFree(b->labels);
+        cudaFree(b->colptr);
+        cudaFree(b->rowidx);
+        cudaFree(b->cvals);
+    }
+    delete b;
+    return 0;
+}
+
+// ---- compute --------------------------------------------------------------------------------
+int32_t twtml_predict(const twtml_model* m, const twtml_batch* b, double* out_pred)
+{
+    TW_TRY(check_pair(m, b, "prediction"));
+    if (!out_pred && b->n > 0) return fail(TWTML_E_INVALID_ARG, "twtml_predict: out_pred is null");
+    twtml_ctx* ctx = m->ctx;
+    Guard g(ctx);
+    if (b->n == 0) return 0;
+    TW_TRY(reserve_scratch(ctx, m, b));
+    TW_TRY(ctx->tmp_a.reserve(sizeof(double) * (size_t)b->n));
+    TW_TRY(run_pass(ctx, m, b, MODE_PREDICT, ctx->tmp_a.as<double>(), nullptr, 0));
+    TW_TRY(fetch_rows(ctx, out_pred, ctx->tmp_a.as<double>(), b->n));
+    TW_CUDA(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int32_t twtml_predict_stats(const twtml_model* m, const twtml_batch* b, double* out_real, double* out_pred_rounded, twtml_stats* out)
+{
+    TW_TRY(check_pair(m, b, "prediction"));
+    if (!out) return fail(TWTML_E_INVALID_ARG, "twtml_predict_stats: out is null");
+    Guard g(m->ctx);
+    return do_predict_stats(m, b, out_real, out_pred_rounded, out);
+}
+
+int32_t twtml_train_on_batch(twtml_model* m, const twtml_batch* b, double* loss_history, int32_t cap, int32_t* iters_run)
+{
+    TW_TRY(check_pair(m, b, "training"));
+    Guard g(m->ctx);
+    return do_train(m, b, false, nullptr, nullptr, nullptr, loss_history, cap, iters_run);
+}
+
+int32_t twtml_step(twtml_model* m, const twtml_batch* b, double* out_real, double* out_pred_rounded, twtml_stats* out,
+                   double* loss_history, int32_t cap, int32_t* iters_run)
+{
+    TW_TRY(check_pair(m, b, "training"));
+    if (!out) return fail(TWTML_E_INVALID_ARG, "twtml_step: out is null");
+    Guard g(m->ctx);
+    return do_train(m, b, true, out_real, out_pred_rounded, out, loss_history, cap, iters_run);
+}
+
+} // extern "C"
