@@ -207,7 +207,7 @@ def main():
 
     # ---- end to end through the C ABI with HOST buffers: ingest (H2D) + stats + train + results (D2H)
     e2e = None
-    if args.workload == "dense_1m" or args.rows:
+    if (args.workload == "dense_1m" or args.rows) and args.e2e_steps > 0:
         Xh, yh = batch.export_dense()                                   # host copy of this rank's rows
         Xp = torch.from_numpy(Xh).pin_memory().numpy()
         del Xh
