@@ -122,7 +122,7 @@ __global__ void __launch_bounds__(kCsrThreads) k_csr_rows(const CsrIterArgs a)
 }
 
 // one warp per column task
-__global__ void __launch_bounds__(256) k_csr_cols(const int* __restrict__ rowidx, const double* __restrict__ cvals,
+static __global__ void __launch_bounds__(256) k_csr_cols(const int* __restrict__ rowidx, const double* __restrict__ cvals,
                                                   const long long* __restrict__ colptr, const int* __restrict__ task_col,
                                                   const long long* __restrict__ task_beg, long long ntasks,
                                                   const double* __restrict__ diff, double* __restrict__ task_part,
@@ -144,7 +144,7 @@ __global__ void __launch_bounds__(256) k_csr_cols(const int* __restrict__ rowidx
 }
 
 // one warp per column: gradSum[j] = sum of its tasks in task order (0 for an empty column)
-__global__ void __launch_bounds__(256) k_csr_fold(const long long* __restrict__ taskptr, const double* __restrict__ task_part,
+static __global__ void __launch_bounds__(256) k_csr_fold(const long long* __restrict__ taskptr, const double* __restrict__ task_part,
                                                   int d, double* __restrict__ g, const TrainState* gate)
 {
     if (gate && gate->done) return;
@@ -161,14 +161,14 @@ __global__ void __launch_bounds__(256) k_csr_fold(const long long* __restrict__ 
 }
 
 // ---- transpose build helpers (ingest time) ---------------------------------------------------
-__global__ void k_iota(int* __restrict__ p, long long n)
+static __global__ void k_iota(int* __restrict__ p, long long n)
 {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) p[i] = (int)i;
 }
 
 // sorted column keys -> colptr[0..d]
-__global__ void k_colptr(const int* __restrict__ keys, long long nnz, int d, long long* __restrict__ colptr)
+static __global__ void k_colptr(const int* __restrict__ keys, long long nnz, int d, long long* __restrict__ colptr)
 {
     const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (e > nnz) return;
@@ -178,7 +178,7 @@ __global__ void k_colptr(const int* __restrict__ keys, long long nnz, int d, lon
 }
 
 // perm -> (row of the entry by binary search in rowptr, value)
-__global__ void k_csc_gather(const int* __restrict__ perm, const long long* __restrict__ rowptr, long long n,
+static __global__ void k_csc_gather(const int* __restrict__ perm, const long long* __restrict__ rowptr, long long n,
                              const double* __restrict__ vals, long long nnz, int* __restrict__ rowidx, double* __restrict__ cvals)
 {
     const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -193,14 +193,14 @@ __global__ void k_csc_gather(const int* __restrict__ perm, const long long* __re
     cvals[e] = vals[src];
 }
 
-__global__ void k_task_count(const long long* __restrict__ colptr, int d, long long* __restrict__ ntasks)
+static __global__ void k_task_count(const long long* __restrict__ colptr, int d, long long* __restrict__ ntasks)
 {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j < d) ntasks[j] = (colptr[j + 1] - colptr[j] + kSeg - 1) / kSeg;
     if (j == d) ntasks[j] = 0;
 }
 
-__global__ void k_task_fill(const long long* __restrict__ colptr, const long long* __restrict__ taskptr, int d,
+static __global__ void k_task_fill(const long long* __restrict__ colptr, const long long* __restrict__ taskptr, int d,
                             int* __restrict__ task_col, long long* __restrict__ task_beg)
 {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;

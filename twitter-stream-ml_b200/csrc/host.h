@@ -48,7 +48,7 @@ struct twtml_ctx {
     ncclComm_t comm = nullptr;
     std::mutex mu;
     // scratch, reused across calls
-    twtml::DevBuf partials, shards, stat_partials, stat_shards, state, loss_hist, out10, tmp_a, tmp_b, gather;
+    twtml::DevBuf partials, shards, stat_partials, stat_shards, state, loss_hist, out10, tmp_a, tmp_b, gather, lower;
     // pinned staging ring for host -> device ingest
     void* pin[2] = {nullptr, nullptr};
     size_t pin_bytes = 0;
@@ -85,6 +85,12 @@ struct twtml_batch {
     long long* colptr = nullptr;
     int* rowidx = nullptr;
     double* cvals = nullptr;
+    long long* taskptr = nullptr;  // column -> its tasks (runs of <= kSeg entries)
+    int* task_col = nullptr;
+    long long* task_beg = nullptr;
+    double* task_part = nullptr;
+    long long ntasks = 0;
+    double* diff = nullptr;        // residuals of the current iteration, n
     twtml::Plan plan{};
 };
 

@@ -13,7 +13,7 @@ namespace twtml {
 
 // grid (ceil(pv/32), spr), block (32, 32).  Thread (x, y): column bx*32+x, slice y of the shard's
 // blocks, summed in block order; then the 32 slice sums are added in slice order.
-__global__ void __launch_bounds__(1024) k_shard_reduce(const double* __restrict__ partials, int pv, Plan plan,
+static __global__ void __launch_bounds__(1024) k_shard_reduce(const double* __restrict__ partials, int pv, Plan plan,
                                                        double* __restrict__ shard_out /* spr x pv */,
                                                        const TrainState* state)
 {
@@ -71,7 +71,7 @@ __device__ __forceinline__ double block_sum_1024(double v, double* sm32)
 
 // One CTA of 1024 threads.  Updaters [U] optimization/Updater.scala: 0 Simple (the reference path),
 // 1 SquaredL2, 2 L1.  a*b+c is deliberately NOT fused here (the JVM does not fuse).
-__global__ void __launch_bounds__(1024) k_update(const UpdateArgs a)
+static __global__ void __launch_bounds__(1024) k_update(const UpdateArgs a)
 {
     __shared__ double sm32[32];
     TrainState* st = a.state;
@@ -129,7 +129,7 @@ __global__ void __launch_bounds__(1024) k_update(const UpdateArgs a)
 }
 
 // regVal before the first iteration = updater.compute(w, 0, 0, 1, regParam)._2 [U]
-__global__ void __launch_bounds__(1024) k_train_init(TrainState* st, const double* w, int d, int updater, double reg,
+static __global__ void __launch_bounds__(1024) k_train_init(TrainState* st, const double* w, int d, int updater, double reg,
                                                      int max_iter)
 {
     __shared__ double sm32[32];
@@ -150,7 +150,7 @@ __global__ void __launch_bounds__(1024) k_train_init(TrainState* st, const doubl
 
 // grid spr, block 256: thread t merges slice t of the shard's block tuples in block order, then
 // thread 0 merges the 256 slice tuples in slice order.
-__global__ void __launch_bounds__(256) k_stats_shard(const double* __restrict__ stat_partials, Plan plan,
+static __global__ void __launch_bounds__(256) k_stats_shard(const double* __restrict__ stat_partials, Plan plan,
                                                      double* __restrict__ shard_out /* spr x kStatStride */)
 {
     __shared__ double sm[256 * kStatStride];
@@ -180,7 +180,7 @@ __global__ void __launch_bounds__(256) k_stats_shard(const double* __restrict__ 
 
 // out10: batch, mse, real_stdev, pred_stdev (Utils.round applied), mse_raw, real_stdev_raw,
 // pred_stdev_raw, real_mean, pred_mean, nonfinite
-__global__ void k_stats_final(const double* __restrict__ shards, int nshards, double* __restrict__ out10)
+static __global__ void k_stats_final(const double* __restrict__ shards, int nshards, double* __restrict__ out10)
 {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     Stat7 tot;

@@ -8,7 +8,7 @@
 namespace twtml {
 
 // one CTA per row: features written coalesced; the pad / label slots are cleared
-__global__ void __launch_bounds__(256) k_synth_dense_x(double* __restrict__ X, long long ldx, int d, uint64_t seed,
+static __global__ void __launch_bounds__(256) k_synth_dense_x(double* __restrict__ X, long long ldx, int d, uint64_t seed,
                                                        long long row0, double inv_sqrt_d, long long n)
 {
     for (long long i = blockIdx.x; i < n; i += gridDim.x) {
@@ -24,7 +24,7 @@ __global__ void __launch_bounds__(256) k_synth_dense_x(double* __restrict__ X, l
 
 // one thread per row: y = sum_j X[r][j] * w*[j] in index order + noise, regenerated from the
 // counters (no read of X), written to the label column
-__global__ void __launch_bounds__(256) k_synth_dense_y(double* __restrict__ X, long long ldx, int d, uint64_t seed,
+static __global__ void __launch_bounds__(256) k_synth_dense_y(double* __restrict__ X, long long ldx, int d, uint64_t seed,
                                                        long long row0, double inv_sqrt_d, long long n)
 {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -59,7 +59,7 @@ __device__ __forceinline__ int synth_csr_row(uint64_t seed, uint64_t r, int d_te
     return u;
 }
 
-__global__ void __launch_bounds__(128) k_synth_csr_count(long long* __restrict__ rownnz, long long n, int d_text,
+static __global__ void __launch_bounds__(128) k_synth_csr_count(long long* __restrict__ rownnz, long long n, int d_text,
                                                          uint64_t seed, long long row0)
 {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -68,7 +68,7 @@ __global__ void __launch_bounds__(128) k_synth_csr_count(long long* __restrict__
     rownnz[i] = synth_csr_row(seed, (uint64_t)(row0 + i), d_text, cols) + 4;
 }
 
-__global__ void __launch_bounds__(128) k_synth_csr_fill(const long long* __restrict__ rowptr, int* __restrict__ colidx,
+static __global__ void __launch_bounds__(128) k_synth_csr_fill(const long long* __restrict__ rowptr, int* __restrict__ colidx,
                                                         double* __restrict__ vals, double* __restrict__ labels,
                                                         long long n, int d_text, uint64_t seed, long long row0)
 {

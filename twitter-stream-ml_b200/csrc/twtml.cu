@@ -330,7 +330,7 @@ static int loss_slot(const twtml_batch* b) { return b->csr ? (int)b->d : (int)b-
 static int reserve_scratch(twtml_ctx* ctx, const twtml_model* m, const twtml_batch* b)
 {
     const int pv = partial_width(b);
-    TW_TRY(ctx->partials.reserve(sizeof(double) * (size_t)std::max<long long>(1, b->plan.nblocks) * pv));
+    TW_TRY(ctx->partials.reserve(sizeof(double) * (size_t)std::max<long long>(1, b->plan.nblocks) * (b->csr ? 2 : pv)));
     TW_TRY(ctx->shards.reserve(sizeof(double) * (size_t)kMaxShards * std::max(1, ctx->world) * pv));
     TW_TRY(ctx->stat_partials.reserve(sizeof(double) * (size_t)std::max<long long>(1, b->plan.nblocks) * kStatStride));
     TW_TRY(ctx->stat_shards.reserve(sizeof(double) * (size_t)kMaxShards * std::max(1, ctx->world) * kStatStride));
@@ -573,7 +573,7 @@ int32_t twtml_destroy(twtml_ctx* ctx)
     cudaStreamSynchronize(ctx->stream);
     if (ctx->comm) nccl_api().CommDestroy(ctx->comm);
     for (DevBuf* b : {&ctx->partials, &ctx->shards, &ctx->stat_partials, &ctx->stat_shards, &ctx->state, &ctx->loss_hist, &ctx->out10,
-                      &ctx->tmp_a, &ctx->tmp_b, &ctx->gather})
+                      &ctx->tmp_a, &ctx->tmp_b, &ctx->gather, &ctx->lower})
         b->release();
     for (int i = 0; i < 2; ++i) {
         if (ctx->pin[i]) cudaFreeHost(ctx->pin[i]);
@@ -833,6 +833,11 @@ int32_t twtml_batch_free(twtml_batch* b)
         cudaFree(b->colptr);
         cudaFree(b->rowidx);
         cudaFree(b->cvals);
+        cudaFree(b->taskptr);
+        cudaFree(b->task_col);
+        cudaFree(b->task_beg);
+        cudaFree(b->task_part);
+        cudaFree(b->diff);
     }
     delete b;
     return 0;

@@ -1,14 +1,354 @@
-// placeholder until the CSR path lands (next commit)
+// twtml_sparse.cu -- CSR micro-batches: ingest (from caller CSR, from raw tweets through the device
+// featuriser, or synthetic), the transpose they carry for the column pass, and the per-iteration
+// launches of csr.cuh.  CUB is used for two pieces of ingest-time plumbing only (a stable radix
+// sort by column to build the transpose, exclusive prefix sums); nothing of it runs per iteration.
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <vector>
+
+#include "csr.cuh"
+#include "featurize.cuh"
 #include "host.h"
+#include "lower_table.h"
+#include "reduce.cuh"
+#include "synth.cuh"
+
 namespace twtml {
-int csr_launch_iter(twtml_ctx*, const twtml_model*, const twtml_batch*, int, double*, double*, int) { return fail(TWTML_E_INVALID_ARG, "CSR path not built"); }
+
+template <class T>
+static int dev_alloc(T** p, size_t count)
+{
+    *p = nullptr;
+    cudaError_t e = cudaMalloc(reinterpret_cast<void**>(p), sizeof(T) * std::max<size_t>(count, 1));
+    if (e != cudaSuccess) return fail(TWTML_E_OOM, "cudaMalloc(%zu bytes): %s", sizeof(T) * count, cudaGetErrorString(e));
+    return 0;
+}
+
+static int exclusive_sum(twtml_ctx* ctx, const long long* in, long long* out, long long n)
+{
+    size_t tmp = 0;
+    TW_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp, in, out, n, ctx->stream));
+    TW_TRY(ctx->gather.reserve(tmp));
+    TW_CUDA(cub::DeviceScan::ExclusiveSum(ctx->gather.p, tmp, in, out, n, ctx->stream));
+    return 0;
+}
+
+static unsigned blocks_for(long long n, int threads) { return (unsigned)std::max<long long>(1, (n + threads - 1) / threads); }
+
+// rowptr / colidx / vals / labels are on the device: build the plan, the transpose and the column tasks
+static int csr_finalize(twtml_ctx* ctx, twtml_batch* b)
+{
+    make_plan(b->n, 1, 1, b->plan); // one shard per rank: the column sums are per rank, not per virtual shard
+    TW_TRY(ctx_global_rows(ctx, b->n, &b->n_global, &b->row0_global));
+    if (b->nnz >= ((long long)1 << 31) || b->n >= ((long long)1 << 31))
+        return fail(TWTML_E_INVALID_ARG, "CSR batch too large for 32-bit entry indices (%lld rows, %lld nnz per GPU)", (long long)b->n, (long long)b->nnz);
+    const int d = (int)b->d;
+    const long long nnz = b->nnz;
+    TW_TRY(dev_alloc(&b->colptr, (size_t)d + 1));
+    TW_TRY(dev_alloc(&b->rowidx, (size_t)nnz));
+    TW_TRY(dev_alloc(&b->cvals, (size_t)nnz));
+    TW_TRY(dev_alloc(&b->taskptr, (size_t)d + 2));
+    TW_TRY(dev_alloc(&b->diff, (size_t)b->n));
+    if (nnz > 0) {
+        int *keys_out = nullptr, *iota = nullptr, *perm = nullptr;
+        TW_TRY(dev_alloc(&keys_out, (size_t)nnz));
+        TW_TRY(dev_alloc(&iota, (size_t)nnz));
+        TW_TRY(dev_alloc(&perm, (size_t)nnz));
+        int rc = 0;
+        do {
+            k_iota<<<blocks_for(nnz, 256), 256, 0, ctx->stream>>>(iota, nnz);
+            int bits = 1;
+            while (((long long)1 << bits) < d) ++bits;
+            size_t tmp = 0;
+            cudaError_t e = cub::DeviceRadixSort::SortPairs(nullptr, tmp, b->colidx, keys_out, iota, perm, (int)nnz, 0, bits, ctx->stream);
+            if (e != cudaSuccess) { rc = fail(TWTML_E_CUDA, "radix sort sizing: %s", cudaGetErrorString(e)); break; }
+            if ((rc = ctx->tmp_a.reserve(tmp))) break;
+            // LSD radix sort is stable: entries of a column keep their CSR (row) order
+            e = cub::DeviceRadixSort::SortPairs(ctx->tmp_a.p, tmp, b->colidx, keys_out, iota, perm, (int)nnz, 0, bits, ctx->stream);
+            if (e != cudaSuccess) { rc = fail(TWTML_E_CUDA, "radix sort: %s", cudaGetErrorString(e)); break; }
+            k_colptr<<<blocks_for(nnz + 1, 256), 256, 0, ctx->stream>>>(keys_out, nnz, d, b->colptr);
+            k_csc_gather<<<blocks_for(nnz, 256), 256, 0, ctx->stream>>>(perm, b->rowptr, b->n, b->vals, nnz, b->rowidx, b->cvals);
+            if (cudaGetLastError() != cudaSuccess) rc = fail(TWTML_E_CUDA, "transpose kernels failed to launch");
+        } while (0);
+        cudaStreamSynchronize(ctx->stream);
+        cudaFree(keys_out);
+        cudaFree(iota);
+        cudaFree(perm);
+        if (rc) return rc;
+    } else {
+        TW_CUDA(cudaMemsetAsync(b->colptr, 0, sizeof(long long) * ((size_t)d + 1), ctx->stream));
+    }
+    long long* ntasks = nullptr;
+    TW_TRY(dev_alloc(&ntasks, (size_t)d + 2));
+    k_task_count<<<blocks_for(d + 1, 256), 256, 0, ctx->stream>>>(b->colptr, d, ntasks);
+    int rc = exclusive_sum(ctx, ntasks, b->taskptr, d + 1);
+    long long total = 0;
+    if (!rc && cudaMemcpyAsync(&total, b->taskptr + d, sizeof(total), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) rc = fail(TWTML_E_CUDA, "task count copy failed");
+    cudaStreamSynchronize(ctx->stream);
+    cudaFree(ntasks);
+    if (rc) return rc;
+    b->ntasks = total;
+    TW_TRY(dev_alloc(&b->task_col, (size_t)total));
+    TW_TRY(dev_alloc(&b->task_beg, (size_t)total));
+    TW_TRY(dev_alloc(&b->task_part, (size_t)total));
+    k_task_fill<<<blocks_for(d, 256), 256, 0, ctx->stream>>>(b->colptr, b->taskptr, d, b->task_col, b->task_beg);
+    TW_CUDA(cudaGetLastError());
+    TW_CUDA(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+static int new_csr(twtml_ctx* ctx, int64_t n, int64_t d, int64_t nnz, twtml_batch** out)
+{
+    twtml_batch* b = new twtml_batch();
+    b->ctx = ctx;
+    b->csr = true;
+    b->n = n;
+    b->d = d;
+    b->nnz = nnz;
+    int rc = dev_alloc(&b->rowptr, (size_t)n + 1);
+    if (!rc) rc = dev_alloc(&b->colidx, (size_t)nnz);
+    if (!rc) rc = dev_alloc(&b->vals, (size_t)nnz);
+    if (!rc) rc = dev_alloc(&b->labels, (size_t)n);
+    if (rc) { twtml_batch_free(b); return rc; }
+    *out = b;
+    return 0;
+}
+
+// ---- per-iteration launches -----------------------------------------------------------------
 int csr_partial_width(const twtml_batch* b) { return (int)b->d + 2; }
-int csr_reduce(twtml_ctx*, const twtml_batch*, double*, const TrainState*) { return fail(TWTML_E_INVALID_ARG, "CSR path not built"); }
+
+int csr_launch_iter(twtml_ctx* ctx, const twtml_model* m, const twtml_batch* b, int mode, double* out_pred, double* out_real,
+                    int iter_override)
+{
+    CsrIterArgs a{};
+    a.rowptr = b->rowptr;
+    a.colidx = b->colidx;
+    a.vals = b->vals;
+    a.labels = b->labels;
+    a.w = m->d_w;
+    a.state = ctx->state.as<TrainState>();
+    a.diff = b->diff;
+    a.partials = ctx->partials.as<double>();
+    a.stat_partials = ctx->stat_partials.as<double>();
+    a.out_pred = out_pred;
+    a.out_real = out_real;
+    a.plan = b->plan;
+    a.frac = m->frac;
+    a.row0_global = (unsigned long long)b->row0_global;
+    a.iter_override = iter_override;
+    const unsigned grid = (unsigned)std::min<long long>(b->plan.nblocks, (long long)ctx->sm_count * 8);
+    if (grid == 0) return 0;
+    switch (mode) {
+    case MODE_TRAIN: k_csr_rows<MODE_TRAIN><<<grid, kCsrThreads, 0, ctx->stream>>>(a); break;
+    case MODE_TRAIN_STATS: k_csr_rows<MODE_TRAIN_STATS><<<grid, kCsrThreads, 0, ctx->stream>>>(a); break;
+    case MODE_PREDICT: k_csr_rows<MODE_PREDICT><<<grid, kCsrThreads, 0, ctx->stream>>>(a); break;
+    default: k_csr_rows<MODE_PREDICT_STATS><<<grid, kCsrThreads, 0, ctx->stream>>>(a); break;
+    }
+    TW_CUDA(cudaGetLastError());
+    return 0;
 }
+
+// column pass + (lossSum, count) fold -> this rank's shard vector [g_0..g_{d-1}, lossSum, count]
+int csr_reduce(twtml_ctx* ctx, const twtml_batch* b, double* shard_out, const TrainState* gate)
+{
+    const int d = (int)b->d;
+    if (b->ntasks > 0) {
+        const unsigned g1 = (unsigned)std::min<long long>((b->ntasks + 7) / 8, (long long)ctx->sm_count * 32);
+        k_csr_cols<<<g1, 256, 0, ctx->stream>>>(b->rowidx, b->cvals, b->colptr, b->task_col, b->task_beg, b->ntasks, b->diff, b->task_part, gate);
+    }
+    const unsigned g2 = (unsigned)std::min<long long>(((long long)d + 7) / 8, (long long)ctx->sm_count * 32);
+    k_csr_fold<<<g2, 256, 0, ctx->stream>>>(b->taskptr, b->task_part, d, shard_out, gate);
+    dim3 grid(1, 1), block(32, 32);
+    k_shard_reduce<<<grid, block, 0, ctx->stream>>>(ctx->partials.as<double>(), 2, b->plan, shard_out + d, gate);
+    TW_CUDA(cudaGetLastError());
+    ctx->prof.other_launches += 3;
+    return 0;
+}
+
+static int lower_table(twtml_ctx* ctx, const uint16_t** out)
+{
+    if (!ctx->lower.p) {
+        std::vector<uint16_t> t(65536);
+        for (int c = 0; c < 65536; ++c) t[c] = (uint16_t)c;
+        for (int i = 0; i < kLowerPairCount; ++i) t[kLowerPairs[i][0]] = kLowerPairs[i][1];
+        TW_TRY(ctx->lower.reserve(sizeof(uint16_t) * 65536));
+        TW_CUDA(cudaMemcpyAsync(ctx->lower.p, t.data(), sizeof(uint16_t) * 65536, cudaMemcpyHostToDevice, ctx->stream));
+        TW_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    *out = ctx->lower.as<uint16_t>();
+    return 0;
+}
+
+} // namespace twtml
+
 using namespace twtml;
+
 extern "C" {
-int32_t twtml_batch_from_tweets(twtml_ctx*, const uint16_t*, const int64_t*, const int32_t*, const int32_t*, const int32_t*, const int32_t*, const int64_t*, const uint8_t*, int64_t, int64_t, int32_t, int32_t, int32_t, uint32_t, twtml_batch**) { return fail(TWTML_E_INVALID_ARG, "not built"); }
-int32_t twtml_batch_from_csr(twtml_ctx*, int64_t, int64_t, const int64_t*, const int32_t*, const double*, const double*, twtml_batch**) { return fail(TWTML_E_INVALID_ARG, "not built"); }
-int32_t twtml_batch_synth_csr(twtml_ctx*, int64_t, int32_t, uint64_t, int64_t, twtml_batch**) { return fail(TWTML_E_INVALID_ARG, "not built"); }
-int32_t twtml_batch_export_csr(const twtml_batch*, int64_t*, int32_t*, double*, double*) { return fail(TWTML_E_INVALID_ARG, "not built"); }
+
+int32_t twtml_batch_from_csr(twtml_ctx* ctx, int64_t n, int64_t d, const int64_t* rowptr, const int32_t* colidx, const double* vals,
+                             const double* labels, twtml_batch** out)
+{
+    if (!ctx || !out) return fail(TWTML_E_INVALID_ARG, "null argument");
+    if (n < 0 || d < 1 || d > ((int64_t)1 << 30) || !rowptr || (n > 0 && !labels)) return fail(TWTML_E_INVALID_ARG, "twtml_batch_from_csr: bad shape or null data");
+    const int64_t nnz = rowptr[n] - rowptr[0];
+    if (rowptr[0] != 0 || nnz < 0 || (nnz > 0 && (!colidx || !vals))) return fail(TWTML_E_INVALID_ARG, "twtml_batch_from_csr: rowptr must start at 0 and be non-decreasing");
+    for (int64_t r = 0; r < n; ++r) { // Vectors.sparse require()s strictly increasing, in-range indices [U]
+        if (rowptr[r + 1] < rowptr[r]) return fail(TWTML_E_INVALID_ARG, "rowptr decreases at row %lld", (long long)r);
+        for (int64_t k = rowptr[r]; k < rowptr[r + 1]; ++k)
+            if (colidx[k] < 0 || colidx[k] >= d || (k > rowptr[r] && colidx[k] <= colidx[k - 1]))
+                return fail(TWTML_E_INVALID_ARG, "row %lld: indices must be strictly increasing and < %lld", (long long)r, (long long)d);
+    }
+    Guard g(ctx);
+    twtml_batch* b = nullptr;
+    TW_TRY(new_csr(ctx, n, d, nnz, &b));
+    int rc = upload_plain(ctx, b->rowptr, rowptr, sizeof(int64_t) * (size_t)(n + 1));
+    if (!rc && nnz) rc = upload_plain(ctx, b->colidx, colidx, sizeof(int32_t) * (size_t)nnz);
+    if (!rc && nnz) rc = upload_plain(ctx, b->vals, vals, sizeof(double) * (size_t)nnz);
+    if (!rc && n) rc = upload_plain(ctx, b->labels, labels, sizeof(double) * (size_t)n);
+    if (!rc) rc = csr_finalize(ctx, b);
+    if (rc) { twtml_batch_free(b); return rc; }
+    *out = b;
+    return 0;
 }
+
+int32_t twtml_batch_synth_csr(twtml_ctx* ctx, int64_t n, int32_t d_text, uint64_t seed, int64_t row0, twtml_batch** out)
+{
+    if (!ctx || !out) return fail(TWTML_E_INVALID_ARG, "null argument");
+    if (n < 0 || d_text < 1) return fail(TWTML_E_INVALID_ARG, "twtml_batch_synth_csr: bad shape");
+    Guard g(ctx);
+    long long *rownnz = nullptr, *rowptr = nullptr;
+    TW_TRY(dev_alloc(&rownnz, (size_t)n + 1));
+    TW_TRY(dev_alloc(&rowptr, (size_t)n + 1));
+    TW_CUDA(cudaMemsetAsync(rownnz, 0, sizeof(long long) * ((size_t)n + 1), ctx->stream));
+    if (n > 0) k_synth_csr_count<<<blocks_for(n, 128), 128, 0, ctx->stream>>>(rownnz, n, d_text, seed, row0);
+    int rc = exclusive_sum(ctx, rownnz, rowptr, n + 1);
+    long long nnz = 0;
+    if (!rc && cudaMemcpyAsync(&nnz, rowptr + n, sizeof(nnz), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) rc = fail(TWTML_E_CUDA, "nnz copy failed");
+    cudaStreamSynchronize(ctx->stream);
+    cudaFree(rownnz);
+    twtml_batch* b = nullptr;
+    if (!rc) rc = new_csr(ctx, n, (int64_t)d_text + 4, nnz, &b);
+    if (!rc) {
+        cudaMemcpyAsync(b->rowptr, rowptr, sizeof(long long) * ((size_t)n + 1), cudaMemcpyDeviceToDevice, ctx->stream);
+        if (n > 0) k_synth_csr_fill<<<blocks_for(n, 128), 128, 0, ctx->stream>>>(b->rowptr, b->colidx, b->vals, b->labels, n, d_text, seed, row0);
+        if (cudaGetLastError() != cudaSuccess) rc = fail(TWTML_E_CUDA, "synthetic CSR generator failed to launch");
+    }
+    cudaStreamSynchronize(ctx->stream);
+    cudaFree(rowptr);
+    if (!rc) rc = csr_finalize(ctx, b);
+    if (rc) { twtml_batch_free(b); return rc; }
+    *out = b;
+    return 0;
+}
+
+int32_t twtml_batch_from_tweets(twtml_ctx* ctx, const uint16_t* text_utf16, const int64_t* text_off, const int32_t* retweet_cnt,
+                                const int32_t* followers, const int32_t* favourites, const int32_t* friends, const int64_t* created_ms,
+                                const uint8_t* is_retweet, int64_t n, int64_t now_ms, int32_t rt_begin, int32_t rt_end,
+                                int32_t num_text_features, uint32_t flags, twtml_batch** out)
+{
+    if (!ctx || !out) return fail(TWTML_E_INVALID_ARG, "null argument");
+    if (n < 0 || num_text_features < 1 || num_text_features > (1 << 30) - 4) return fail(TWTML_E_INVALID_ARG, "twtml_batch_from_tweets: bad sizes");
+    if (n > 0 && (!text_off || !retweet_cnt || !followers || !favourites || !friends || !created_ms || !is_retweet))
+        return fail(TWTML_E_INVALID_ARG, "twtml_batch_from_tweets: null column");
+    const int64_t units = n > 0 ? text_off[n] : 0;
+    if (n > 0 && (text_off[0] != 0 || units < 0 || (units > 0 && !text_utf16))) return fail(TWTML_E_INVALID_ARG, "twtml_batch_from_tweets: bad text offsets");
+    Guard g(ctx);
+    const int F = num_text_features;
+    twtml_batch* b = nullptr;
+    if (n == 0) {
+        TW_TRY(new_csr(ctx, 0, (int64_t)F + 4, 0, &b));
+        TW_CUDA(cudaMemsetAsync(b->rowptr, 0, sizeof(long long), ctx->stream));
+        int rc = csr_finalize(ctx, b);
+        if (rc) { twtml_batch_free(b); return rc; }
+        *out = b;
+        return 0;
+    }
+    // device copies of the tweet columns
+    uint16_t* d_text = nullptr;
+    long long *d_off = nullptr, *d_created = nullptr, *keep = nullptr, *rownnz = nullptr, *krow = nullptr, *eoff = nullptr;
+    int *d_rc = nullptr, *d_fo = nullptr, *d_fa = nullptr, *d_fr = nullptr, *pair_idx = nullptr, *pair_cnt = nullptr, *d_maxlen = nullptr;
+    uint8_t* d_rt = nullptr;
+    std::vector<void*> owned;
+    auto cleanup = [&]() { for (void* p : owned) cudaFree(p); };
+#define TW_OWN(call, ptrvar) do { int rc_ = (call); if (rc_) { cleanup(); return rc_; } owned.push_back(ptrvar); } while (0)
+#define TW_DO(call) do { int rc_ = (call); if (rc_) { cleanup(); return rc_; } } while (0)
+    TW_OWN(dev_alloc(&d_text, (size_t)units), d_text);
+    TW_OWN(dev_alloc(&d_off, (size_t)n + 1), d_off);
+    TW_OWN(dev_alloc(&d_created, (size_t)n), d_created);
+    TW_OWN(dev_alloc(&d_rc, (size_t)n), d_rc);
+    TW_OWN(dev_alloc(&d_fo, (size_t)n), d_fo);
+    TW_OWN(dev_alloc(&d_fa, (size_t)n), d_fa);
+    TW_OWN(dev_alloc(&d_fr, (size_t)n), d_fr);
+    TW_OWN(dev_alloc(&d_rt, (size_t)n), d_rt);
+    TW_OWN(dev_alloc(&pair_idx, (size_t)units), pair_idx);
+    TW_OWN(dev_alloc(&pair_cnt, (size_t)units), pair_cnt);
+    TW_OWN(dev_alloc(&keep, (size_t)n + 1), keep);
+    TW_OWN(dev_alloc(&rownnz, (size_t)n + 1), rownnz);
+    TW_OWN(dev_alloc(&krow, (size_t)n + 1), krow);
+    TW_OWN(dev_alloc(&eoff, (size_t)n + 1), eoff);
+    TW_OWN(dev_alloc(&d_maxlen, 1), d_maxlen);
+    if (units) TW_DO(upload_plain(ctx, d_text, text_utf16, sizeof(uint16_t) * (size_t)units));
+    TW_DO(upload_plain(ctx, d_off, text_off, sizeof(int64_t) * (size_t)(n + 1)));
+    TW_DO(upload_plain(ctx, d_created, created_ms, sizeof(int64_t) * (size_t)n));
+    TW_DO(upload_plain(ctx, d_rc, retweet_cnt, sizeof(int32_t) * (size_t)n));
+    TW_DO(upload_plain(ctx, d_fo, followers, sizeof(int32_t) * (size_t)n));
+    TW_DO(upload_plain(ctx, d_fa, favourites, sizeof(int32_t) * (size_t)n));
+    TW_DO(upload_plain(ctx, d_fr, friends, sizeof(int32_t) * (size_t)n));
+    TW_DO(upload_plain(ctx, d_rt, is_retweet, (size_t)n));
+
+    cudaMemsetAsync(d_maxlen, 0, sizeof(int), ctx->stream);
+    k_feat_maxlen<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(d_off, n, d_maxlen);
+    int maxlen = 0;
+    cudaMemcpyAsync(&maxlen, d_maxlen, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream);
+    if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) { cleanup(); return fail(TWTML_E_CUDA, "tweet upload failed: %s", cudaGetErrorString(cudaGetLastError())); }
+    if (maxlen > kMaxTerms + 1) { cleanup(); return fail(TWTML_E_INVALID_ARG, "a tweet has %d UTF-16 units; the featuriser takes at most %d", maxlen, kMaxTerms + 1); }
+
+    const uint16_t* lower = nullptr;
+    if (flags & TWTML_FLAG_LOWERCASE) TW_DO(lower_table(ctx, &lower));
+    TweetCols tc{d_text, d_off, d_rc, d_fo, d_fa, d_fr, d_created, d_rt};
+    cudaMemsetAsync(keep + n, 0, sizeof(long long), ctx->stream);
+    cudaMemsetAsync(rownnz + n, 0, sizeof(long long), ctx->stream);
+    const unsigned gridA = (unsigned)std::min<long long>((n + kFeatWarps - 1) / kFeatWarps, (long long)ctx->sm_count * 16);
+    k_feat_terms<<<gridA, kFeatWarps * 32, 0, ctx->stream>>>(tc, n, rt_begin, rt_end, F, lower, pair_idx, pair_cnt, keep, rownnz);
+    TW_DO(exclusive_sum(ctx, keep, krow, n + 1));
+    TW_DO(exclusive_sum(ctx, rownnz, eoff, n + 1));
+    long long tot[2] = {0, 0};
+    cudaMemcpyAsync(&tot[0], krow + n, sizeof(long long), cudaMemcpyDeviceToHost, ctx->stream);
+    cudaMemcpyAsync(&tot[1], eoff + n, sizeof(long long), cudaMemcpyDeviceToHost, ctx->stream);
+    if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) { cleanup(); return fail(TWTML_E_CUDA, "featuriser failed: %s", cudaGetErrorString(cudaGetLastError())); }
+    const long long n_kept = tot[0], nnz = tot[1];
+    TW_DO(new_csr(ctx, n_kept, (int64_t)F + 4, nnz, &b));
+    const unsigned gridB = (unsigned)std::min<long long>((n + 3) / 4, (long long)ctx->sm_count * 16);
+    k_feat_pack<<<gridB, 128, 0, ctx->stream>>>(tc, n, now_ms, F, pair_idx, pair_cnt, keep, krow, rownnz, eoff, b->rowptr, b->colidx, b->vals, b->labels);
+    cudaMemcpyAsync(b->rowptr + n_kept, &tot[1], sizeof(long long), cudaMemcpyHostToDevice, ctx->stream);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cleanup();
+#undef TW_OWN
+#undef TW_DO
+    int rc = e == cudaSuccess ? 0 : fail(TWTML_E_CUDA, "featuriser pack failed: %s", cudaGetErrorString(e));
+    if (!rc) rc = csr_finalize(ctx, b);
+    if (rc) { twtml_batch_free(b); return rc; }
+    *out = b;
+    return 0;
+}
+
+int32_t twtml_batch_export_csr(const twtml_batch* b, int64_t* rowptr, int32_t* colidx, double* vals, double* labels)
+{
+    if (!b || !rowptr) return fail(TWTML_E_INVALID_ARG, "null argument");
+    if (!b->csr) return fail(TWTML_E_INVALID_ARG, "twtml_batch_export_csr on a dense batch");
+    twtml_ctx* ctx = b->ctx;
+    Guard g(ctx);
+    TW_CUDA(cudaMemcpyAsync(rowptr, b->rowptr, sizeof(int64_t) * (size_t)(b->n + 1), cudaMemcpyDeviceToHost, ctx->stream));
+    if (b->nnz && colidx) TW_CUDA(cudaMemcpyAsync(colidx, b->colidx, sizeof(int32_t) * (size_t)b->nnz, cudaMemcpyDeviceToHost, ctx->stream));
+    if (b->nnz && vals) TW_CUDA(cudaMemcpyAsync(vals, b->vals, sizeof(double) * (size_t)b->nnz, cudaMemcpyDeviceToHost, ctx->stream));
+    if (b->n && labels) TW_CUDA(cudaMemcpyAsync(labels, b->labels, sizeof(double) * (size_t)b->n, cudaMemcpyDeviceToHost, ctx->stream));
+    TW_CUDA(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+} // extern "C"
