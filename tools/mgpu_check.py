@@ -1,0 +1,66 @@
+#!/usr/bin/env python3
+"""Multi-GPU parity check, run under torchrun (one rank per GPU):
+   the same micro-batch, row-sharded over G GPUs, must give the SAME BITS as on one GPU when
+   n % 8 == 0 (fixed virtual-shard reduction order), must match the CPU oracle to 1e-6, and the
+   statistics must be those of the whole batch on every rank.  Prints one line 'MGPU OK ...'."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import twtml_b200 as tw
+from twtml_b200.dist import ranked_context, row_range
+from oracle import oracle_c
+
+
+def main():
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    rank, world = dist.get_rank(), dist.get_world_size()
+    ctx = ranked_context(local)
+    results = {}
+    for n, d, iters in [(8 * 1000, 1004, 12), (4096, 128, 10), (8 * 333 + 3, 1004, 5)]:
+        X, y = oracle_c.synth_dense(n, d, seed=5)
+        y = np.round(y * 300 + 400)
+        w0 = np.linspace(-0.1, 0.1, d)
+        lo, hi = row_range(n, rank, world)
+        m = (tw.StreamingLinearRegressionWithSGD(ctx=ctx).setNumIterations(iters).setStepSize(0.1)
+             .setConvergenceTol(0.0).setInitialWeights(tw.Vectors.dense(w0)))
+        b = ctx.batch_from_dense(X[lo:hi], y[lo:hi])
+        st, real, pred = m.step(b)
+        w = m.latestModel().weights.toArray()
+        w_ref, h_ref = oracle_c.sgd(y, d, w0, X=X, step_size=0.1, num_iterations=iters, convergence_tol=0.0)
+        s_ref, _, rnd_ref = oracle_c.predict_stats(y, d, w0, X=X)
+        assert np.max(np.abs(w - w_ref)) / np.max(np.abs(w_ref)) < 1e-6
+        assert np.max(np.abs(m.lastLossHistory - h_ref) / np.abs(h_ref)) < 1e-6
+        assert st["batch"] == n and st["mse"] == s_ref["mse"] and st["real_stdev"] == s_ref["real_stdev"] and st["pred_stdev"] == s_ref["pred_stdev"]
+        assert np.array_equal(pred, rnd_ref[lo:hi]) and np.array_equal(real, y[lo:hi])
+        # every rank holds the same weights, bit for bit
+        wt = torch.from_numpy(w).cuda()
+        w0t = wt.clone()
+        dist.broadcast(w0t, src=0)
+        assert torch.equal(wt, w0t), "ranks disagree on the weights"
+        results[(n, d)] = w
+        # sparse form of a small batch too (one shard per rank)
+        if d == 128:
+            rp, ci, va, la = oracle_c.synth_csr(n, 500, seed=9)
+            ms = (tw.StreamingLinearRegressionWithSGD(ctx=ctx).setNumIterations(6).setStepSize(0.005)
+                  .setConvergenceTol(0.0).setInitialWeights(tw.Vectors.zeros(504)))
+            rps = rp[lo:hi + 1] - rp[lo]
+            bs = ctx.batch_from_csr(hi - lo, 504, rps, ci[rp[lo]:rp[hi]], va[rp[lo]:rp[hi]], la[lo:hi])
+            ms.trainOnBatch(bs)
+            ws_ref, hs_ref = oracle_c.sgd(la, 504, np.zeros(504), csr=(rp, ci, va), step_size=0.005, num_iterations=6, convergence_tol=0.0)
+            assert np.max(np.abs(ms.latestModel().weights.toArray() - ws_ref)) / np.max(np.abs(ws_ref)) < 1e-6
+    if rank == 0:
+        np.savez(os.environ.get("MGPU_OUT", "/tmp/mgpu_w%d.npz" % world), **{"%d_%d" % k: v for k, v in results.items()})
+        print("MGPU OK world=%d" % world, flush=True)
+    ctx.close()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

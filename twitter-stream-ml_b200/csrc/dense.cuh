@@ -99,12 +99,14 @@ struct IterSmem {
     static constexpr unsigned kStages = ((kGbuf + kIterThreads * 16) + 127) & ~127u;
 };
 
-template <int CP, int MODE>
+// RL1: one row lane (c2p == 512 or CP > 1): the common wide-row case, with compile-time offsets.
+template <int CP, int MODE, bool RL1>
 __global__ void __launch_bounds__(kIterThreads, (CP == 1 && (MODE == MODE_TRAIN || MODE == MODE_PREDICT)) ? 2 : 1) k_dense_iter(const DenseIterArgs a)
 {
     constexpr bool kTrain = (MODE == MODE_TRAIN || MODE == MODE_TRAIN_STATS);
     constexpr bool kStats = (MODE == MODE_TRAIN_STATS || MODE == MODE_PREDICT_STATS);
     constexpr int RPT = 4 / CP;
+    static_assert(CP == 1 || RL1, "several column passes imply one row lane");
     if (kTrain && a.state->done) return;
 
     extern __shared__ __align__(128) unsigned char smem[];
@@ -116,34 +118,46 @@ __global__ void __launch_bounds__(kIterThreads, (CP == 1 && (MODE == MODE_TRAIN 
     unsigned char* stages = smem + IterSmem::kStages;
 
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-    const int d = a.d, C2 = a.c2, RL = a.rl, R = RPT * RL, S = a.nstages;
+    const int d = a.d, C2 = a.c2, S = a.nstages;
+    const int RL = RL1 ? 1 : a.rl;
+    const int R = RPT * RL;
     const long long ldx = a.ldx;
     const int pv = (int)ldx + 2;
-    const int rl = (CP == 1) ? t / a.c2p : 0;
-    const int wpr = (CP == 1) ? a.c2p / 32 : kIterWarps; // warps per row lane
-    const bool lane_live = rl < RL;
+    const int rl = RL1 ? 0 : t / a.c2p;
+    const int wpr = RL1 ? kIterWarps : a.c2p / 32; // warps per row lane
 
+    // Column ownership.  A thread without a column (past the row's end, or in an unused row lane)
+    // shadows column pair 0 of row lane 0 with zero weights: it loads valid finite data, adds 0 to
+    // the dot products and never stores its gradient, so the hot loop carries no predicates.
     int col2[CP];
     double w0[CP], w1[CP];
-    bool live[CP], fix[CP];
+    bool live[CP];
+    unsigned xoff[CP]; // byte offset of this thread's first row inside a stage
 #pragma unroll
     for (int p = 0; p < CP; ++p) {
-        col2[p] = (CP == 1) ? (t - rl * a.c2p) : (t + p * kIterThreads);
-        live[p] = lane_live && col2[p] < C2;
+        col2[p] = RL1 ? (t + p * kIterThreads) : (t - rl * a.c2p);
+        live[p] = rl < RL && col2[p] < C2;
         const int c0 = 2 * col2[p];
+        // the label / pad columns carry zero weights: they add exactly 0 to x.w; their gradient slots are never read
         w0[p] = (live[p] && c0 < d) ? a.w[c0] : 0.0;
         w1[p] = (live[p] && c0 + 1 < d) ? a.w[c0 + 1] : 0.0;
-        fix[p] = live[p] && (c0 + 1 >= d); // this pair touches the label / pad columns
+        xoff[p] = live[p] ? (unsigned)(((long long)rl * ldx + c0) * 8) : 0u;
     }
+    const unsigned rstride = (unsigned)((long long)RL * ldx * 8); // between a thread's consecutive rows
+    const int drow = (RL1 || rl < RL) ? rl : 0;
 
     const unsigned long long iter_seed =
         splitmix64((unsigned long long)(42 + (a.iter_override > 0 ? a.iter_override : (kTrain ? a.state->iter : 0))));
     const bool sampling = kTrain && a.frac < 1.0;
 
+    // rows beyond a ragged stage's end are read as whatever the slot held before: make that finite
+    for (unsigned o = (unsigned)t * 16; o < (unsigned)S * a.stage_stride; o += kIterThreads * 16)
+        *reinterpret_cast<double2*>(stages + o) = make_double2(0.0, 0.0);
     if (t == 0) {
         for (int s = 0; s < S; ++s) mbar_init(&full[s], 1);
         mbar_fence_init();
     }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); // generic writes above, async-proxy (TMA) writes next
     __syncthreads();
 
     // ---- producer cursor (thread 0 only), S stages ahead of the consumer cursor
@@ -172,16 +186,18 @@ __global__ void __launch_bounds__(kIterThreads, (CP == 1 && (MODE == MODE_TRAIN 
     double my_loss = 0.0, my_cnt = 0.0; // threads t < R: their row of every stage
     Stat7 my_stat;
     stat_zero(my_stat);
+    // thread t < R finishes row t of each stage: that is row lane t % RL, k-th row t / RL
+    const double* my_wpart = wpart + ((RL1 ? 0 : (t % RL) * wpr) * 4 + (RL1 ? t : t / RL));
+    const unsigned yoff = (unsigned)(((long long)t * ldx + d) * 8);
 
     int slot = 0;
     unsigned parity = 0;
+    const unsigned char* st = stages;
     for (long long blk = blockIdx.x; blk < a.plan.nblocks; blk += gridDim.x) {
         long long row0;
         int nrows;
         block_geom(a.plan, blk, row0, nrows);
         for (int r0 = 0; r0 < nrows; r0 += R) {
-            const int nr = min(R, nrows - r0);
-            const unsigned char* st = stages + (size_t)slot * a.stage_stride;
             mbar_wait(&full[slot], parity);
 
             // ---- phase 1: registers <- smem, partial dots
@@ -189,17 +205,10 @@ __global__ void __launch_bounds__(kIterThreads, (CP == 1 && (MODE == MODE_TRAIN 
             double part[RPT];
 #pragma unroll
             for (int k = 0; k < RPT; ++k) {
-                const int r = k * RL + rl;
                 part[k] = 0.0;
 #pragma unroll
                 for (int p = 0; p < CP; ++p) {
-                    double2 v = make_double2(0.0, 0.0);
-                    if (live[p] && r < nr)
-                        v = *reinterpret_cast<const double2*>(st + ((size_t)r * ldx + 2 * col2[p]) * 8);
-                    if (fix[p]) { // label / pad columns take no part in the dot product or the gradient
-                        if (2 * col2[p] >= d) v.x = 0.0;
-                        v.y = 0.0;
-                    }
+                    const double2 v = *reinterpret_cast<const double2*>(st + xoff[p] + k * rstride);
                     x[k][p] = v;
                     part[k] = fma(v.x, w0[p], part[k]);
                     part[k] = fma(v.y, w1[p], part[k]);
@@ -214,12 +223,16 @@ __global__ void __launch_bounds__(kIterThreads, (CP == 1 && (MODE == MODE_TRAIN 
 
             // ---- one thread per row: finish the dot product, residual, loss, statistics
             if (t < R) {
-                const int rr = t % RL, kk = t / RL;
                 double diff = 0.0;
-                if (t < nr) {
+                if (t < nrows - r0) {
                     double dot = 0.0;
-                    for (int q = 0; q < wpr; ++q) dot += wpart[(rr * wpr + q) * 4 + kk];
-                    const double y = *reinterpret_cast<const double*>(st + ((size_t)t * ldx + d) * 8);
+                    if (RL1) {
+#pragma unroll
+                        for (int q = 0; q < kIterWarps; ++q) dot += my_wpart[q * 4];
+                    } else {
+                        for (int q = 0; q < wpr; ++q) dot += my_wpart[q * 4];
+                    }
+                    const double y = *reinterpret_cast<const double*>(st + yoff);
                     const long long lrow = row0 + r0 + t;
                     if (kTrain) {
                         const bool keep = !sampling || row_sampled(iter_seed, a.row0_global + (unsigned long long)lrow, a.frac);
@@ -238,7 +251,7 @@ __global__ void __launch_bounds__(kIterThreads, (CP == 1 && (MODE == MODE_TRAIN 
                         a.out_pred[lrow] = dot + 0.0;
                     }
                 }
-                if (kTrain) sdiff[t] = diff;
+                if (kTrain) sdiff[t] = diff; // 0 for rows past the end: they add +-0 to the gradient
             }
             __syncthreads(); // (B) the stage is no longer read from here on
 
@@ -246,32 +259,40 @@ __global__ void __launch_bounds__(kIterThreads, (CP == 1 && (MODE == MODE_TRAIN 
 
             // ---- phase 2: gradient from the registers of phase 1
             if (kTrain) {
+                double df[RPT];
+                if (RL1 && RPT == 4) {
+                    const double2 d01 = *reinterpret_cast<const double2*>(sdiff), d23 = *reinterpret_cast<const double2*>(sdiff + 2);
+                    df[0] = d01.x; df[1] = d01.y; df[2 % RPT] = d23.x; df[3 % RPT] = d23.y;
+                } else {
+#pragma unroll
+                    for (int k = 0; k < RPT; ++k) df[k] = sdiff[k * RL + drow];
+                }
 #pragma unroll
                 for (int k = 0; k < RPT; ++k) {
-                    const double df = sdiff[lane_live ? k * RL + rl : 0];
 #pragma unroll
                     for (int p = 0; p < CP; ++p) {
-                        g0[p] = fma(df, x[k][p].x, g0[p]);
-                        g1[p] = fma(df, x[k][p].y, g1[p]);
+                        g0[p] = fma(df[k], x[k][p].x, g0[p]);
+                        g1[p] = fma(df[k], x[k][p].y, g1[p]);
                     }
                 }
             }
-            if (++slot == S) { slot = 0; parity ^= 1u; }
+            st += a.stage_stride;
+            if (++slot == S) { slot = 0; parity ^= 1u; st = stages; }
         }
 
         // ---- end of the row block: write its partial vector
         if (kTrain) {
             double* out = a.partials + blk * (long long)pv;
-            if (RL == 1) {
+            if (RL1) {
 #pragma unroll
                 for (int p = 0; p < CP; ++p)
                     if (live[p]) *reinterpret_cast<double2*>(out + 2 * col2[p]) = make_double2(g0[p], g1[p]);
-            } else { // CP == 1: fold the row lanes in lane order
-                if (lane_live) *reinterpret_cast<double2*>(gbuf + 2 * t) = make_double2(g0[0], g1[0]);
+            } else { // fold the row lanes in lane order
+                if (live[0]) *reinterpret_cast<double2*>(gbuf + 2 * t) = make_double2(g0[0], g1[0]);
             }
             if (t < R) { sred[2 * t] = my_loss; sred[2 * t + 1] = my_cnt; }
             __syncthreads();
-            if (RL > 1 && rl == 0 && live[0]) {
+            if (!RL1 && rl == 0 && live[0]) {
                 double2 acc = make_double2(0.0, 0.0);
                 for (int q = 0; q < RL; ++q) {
                     const double2 v = *reinterpret_cast<const double2*>(gbuf + 2 * (q * a.c2p + col2[0]));
@@ -289,7 +310,7 @@ __global__ void __launch_bounds__(kIterThreads, (CP == 1 && (MODE == MODE_TRAIN 
 #pragma unroll
             for (int p = 0; p < CP; ++p) g0[p] = g1[p] = 0.0;
             my_loss = my_cnt = 0.0;
-            if (kStats || RL > 1) __syncthreads(); // sred / gbuf are reused below / by the next block
+            if (kStats || !RL1) __syncthreads(); // sred / gbuf are reused below / by the next block
         }
         if (kStats) {
             if (t < R) stat_store(sred + t * kStatStride, my_stat);

@@ -127,11 +127,11 @@ void make_plan(int64_t n_local, int spr, int R, Plan& p)
 // ---------------------------------------------------------------------------------------------
 // iteration-kernel dispatch
 // ---------------------------------------------------------------------------------------------
-template <int CP, int MODE>
+template <int CP, int MODE, bool RL1>
 static int launch_iter_t(twtml_ctx* ctx, const DenseCfg& c, const DenseIterArgs& a)
 {
     static bool attr_set[16] = {false};
-    auto kern = k_dense_iter<CP, MODE>;
+    auto kern = k_dense_iter<CP, MODE, RL1>;
     if (!attr_set[ctx->device & 15]) {
         TW_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_set[ctx->device & 15] = true;
@@ -144,22 +144,22 @@ static int launch_iter_t(twtml_ctx* ctx, const DenseCfg& c, const DenseIterArgs&
     return 0;
 }
 
-template <int CP>
+template <int CP, bool RL1>
 static int launch_iter_cp(twtml_ctx* ctx, const DenseCfg& c, const DenseIterArgs& a, int mode)
 {
     switch (mode) {
-    case MODE_TRAIN: return launch_iter_t<CP, MODE_TRAIN>(ctx, c, a);
-    case MODE_TRAIN_STATS: return launch_iter_t<CP, MODE_TRAIN_STATS>(ctx, c, a);
-    case MODE_PREDICT: return launch_iter_t<CP, MODE_PREDICT>(ctx, c, a);
-    default: return launch_iter_t<CP, MODE_PREDICT_STATS>(ctx, c, a);
+    case MODE_TRAIN: return launch_iter_t<CP, MODE_TRAIN, RL1>(ctx, c, a);
+    case MODE_TRAIN_STATS: return launch_iter_t<CP, MODE_TRAIN_STATS, RL1>(ctx, c, a);
+    case MODE_PREDICT: return launch_iter_t<CP, MODE_PREDICT, RL1>(ctx, c, a);
+    default: return launch_iter_t<CP, MODE_PREDICT_STATS, RL1>(ctx, c, a);
     }
 }
 
 static int launch_iter(twtml_ctx* ctx, const DenseCfg& c, const DenseIterArgs& a, int mode)
 {
-    if (c.cp == 1) return launch_iter_cp<1>(ctx, c, a, mode);
-    if (c.cp == 2) return launch_iter_cp<2>(ctx, c, a, mode);
-    return launch_iter_cp<4>(ctx, c, a, mode);
+    if (c.cp == 1) return c.rl == 1 ? launch_iter_cp<1, true>(ctx, c, a, mode) : launch_iter_cp<1, false>(ctx, c, a, mode);
+    if (c.cp == 2) return launch_iter_cp<2, true>(ctx, c, a, mode);
+    return launch_iter_cp<4, true>(ctx, c, a, mode);
 }
 
 // sparse side (twtml_sparse.cu)
@@ -224,7 +224,7 @@ int staged_upload(twtml_ctx* ctx, void* dst, size_t unit_bytes, int64_t n_units,
     for (int64_t u0 = 0; u0 < n_units; u0 += per, ++k) {
         const int64_t nu = std::min(per, n_units - u0);
         const int bi = k & 1;
-        if (k >= 2) TW_CUDA(cudaEventSynchronize(ctx->pin_ev[bi]));
+        TW_CUDA(cudaEventSynchronize(ctx->pin_ev[bi])); // the last copy out of this buffer (maybe an earlier call's) is done
         pack(static_cast<char*>(ctx->pin[bi]), u0, nu);
         TW_CUDA(cudaMemcpyAsync(static_cast<char*>(dst) + (size_t)u0 * unit_bytes, ctx->pin[bi], (size_t)nu * unit_bytes,
                                 cudaMemcpyHostToDevice, ctx->stream));
