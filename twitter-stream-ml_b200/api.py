@@ -10,6 +10,7 @@ registration order, as Spark Streaming's JobScheduler does.  All arithmetic happ
 the GPU; nothing here computes a dot product, a gradient or a statistic.
 """
 import ctypes as C
+import weakref
 
 import numpy as np
 
@@ -32,6 +33,7 @@ class Context:
             buf = (C.c_uint8 * _lib.NCCL_ID_BYTES).from_buffer_copy(bytes(nccl_id))
             check(L.twtml_create_ranked(device, rank, world_size, buf, _lib.NCCL_ID_BYTES, C.byref(self._h)))
         self.device, self.rank, self.world_size = device, rank, world_size
+        self._children = weakref.WeakSet()     # live Batch / model wrappers: freed before the context goes
 
     @staticmethod
     def nccl_unique_id():
@@ -49,7 +51,9 @@ class Context:
 
     def close(self):
         if self._h:
-            _lib.lib().twtml_destroy(self._h)
+            for ch in list(self._children):
+                ch.free()
+            check(_lib.lib().twtml_destroy(self._h))
             self._h = C.c_void_p()
 
     def __enter__(self):
@@ -108,6 +112,7 @@ class Batch:
         n, d, nnz, csr = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int32()
         check(_lib.lib().twtml_batch_info(handle, C.byref(n), C.byref(d), C.byref(nnz), C.byref(csr)))
         self.n, self.d, self.nnz, self.is_csr = n.value, d.value, nnz.value, bool(csr.value)
+        ctx._children.add(self)
 
     def count(self):
         return self.n
@@ -272,11 +277,23 @@ class StreamingLinearRegressionWithSGD:
 
     def __init__(self, stepSize=0.1, numIterations=50, miniBatchFraction=1.0, ctx=None):
         self.ctx = ctx if ctx is not None else Context(0)
+        self.ctx._children.add(self)
         self._m = None
         self._params = dict(step=stepSize, iters=numIterations, frac=miniBatchFraction, tol=0.001, reg=0.0, updater=0)
         self._w0 = None
         self.lastLossHistory = np.zeros(0)
         self.lastStats = None
+
+    def free(self):
+        if self._m is not None:
+            _lib.lib().twtml_model_free(self._m)
+            self._m = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
 
     # ---- setters (return this.type)
     def setStepSize(self, v):

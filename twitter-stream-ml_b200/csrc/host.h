@@ -47,6 +47,7 @@ struct twtml_ctx {
     cudaStream_t stream = nullptr;
     ncclComm_t comm = nullptr;
     std::mutex mu;
+    int live_handles = 0; // models + batches created on this context and not yet freed
     // scratch, reused across calls
     twtml::DevBuf partials, shards, stat_partials, stat_shards, state, loss_hist, out10, tmp_a, tmp_b, gather, lower;
     // pinned staging ring for host -> device ingest
@@ -99,6 +100,14 @@ namespace twtml {
 int upload_plain(twtml_ctx* ctx, void* dst, const void* src, size_t bytes);
 int ctx_global_rows(twtml_ctx* ctx, int64_t n_local, int64_t* n_global, int64_t* row0);
 void make_plan(int64_t n_local, int spr, int R, Plan& p);
+void batch_free_locked(twtml_batch* b);
+// launch shape of the dense iteration kernel for a feature width
+struct DenseCfg {
+    int cp, c2, c2p, rl, R, nstages, grid_per_sm;
+    unsigned stage_stride;
+    size_t smem;
+};
+int dense_cfg(int64_t d, DenseCfg& c);
 struct Guard {
     std::lock_guard<std::mutex> lk;
     explicit Guard(twtml_ctx* c) : lk(c->mu) { cudaSetDevice(c->device); }

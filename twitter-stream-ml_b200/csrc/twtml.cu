@@ -69,13 +69,7 @@ void DevBuf::release()
 // ---------------------------------------------------------------------------------------------
 // plans
 // ---------------------------------------------------------------------------------------------
-struct DenseCfg {
-    int cp, c2, c2p, rl, R, nstages, grid_per_sm;
-    unsigned stage_stride;
-    size_t smem;
-};
-
-static int dense_cfg(int64_t d, DenseCfg& c)
+int dense_cfg(int64_t d, DenseCfg& c)
 {
     const int64_t ldx = (d + 2) & ~(int64_t)1; // round_up(d + 1, 2)
     const int64_t c2 = ldx / 2;
@@ -491,6 +485,17 @@ static int do_train(twtml_model* m, const twtml_batch* b, bool with_stats, doubl
     return 0;
 }
 
+// caller holds the context lock (or is the only owner)
+void batch_free_locked(twtml_batch* b)
+{
+    cudaStreamSynchronize(b->ctx->stream);
+    for (void* p : {(void*)b->X, (void*)b->rowptr, (void*)b->colidx, (void*)b->vals, (void*)b->labels, (void*)b->colptr, (void*)b->rowidx,
+                    (void*)b->cvals, (void*)b->taskptr, (void*)b->task_col, (void*)b->task_beg, (void*)b->task_part, (void*)b->diff})
+        cudaFree(p);
+    b->ctx->live_handles -= 1;
+    delete b;
+}
+
 } // namespace twtml
 
 using namespace twtml;
@@ -569,6 +574,11 @@ int32_t twtml_create_ranked(int32_t device, int32_t rank, int32_t world_size, co
 int32_t twtml_destroy(twtml_ctx* ctx)
 {
     if (!ctx) return 0;
+    {
+        std::lock_guard<std::mutex> lk(ctx->mu);
+        if (ctx->live_handles != 0)
+            return fail(TWTML_E_INVALID_ARG, "twtml_destroy: %d models/batches of this context are still alive; free them first", ctx->live_handles);
+    }
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     if (ctx->comm) nccl_api().CommDestroy(ctx->comm);
@@ -619,6 +629,7 @@ int32_t twtml_model_create(twtml_ctx* ctx, int64_t num_features, twtml_model** o
     m->h_w.assign((size_t)num_features, 0.0);
     cudaError_t e = cudaMalloc(&m->d_w, sizeof(double) * (size_t)(num_features + 2));
     if (e != cudaSuccess) { delete m; return fail(TWTML_E_OOM, "cudaMalloc weights: %s", cudaGetErrorString(e)); }
+    ctx->live_handles += 1;
     *out = m;
     return 0;
 }
@@ -630,6 +641,7 @@ int32_t twtml_model_free(twtml_model* m)
         Guard g(m->ctx);
         cudaStreamSynchronize(m->ctx->stream);
         cudaFree(m->d_w);
+        m->ctx->live_handles -= 1;
     }
     delete m;
     return 0;
@@ -720,6 +732,7 @@ static int32_t new_dense(twtml_ctx* ctx, int64_t n, int64_t d, twtml_batch** out
     }
     int rc = ctx_global_rows(ctx, n, &b->n_global, &b->row0_global);
     if (rc) { cudaFree(b->X); delete b; return rc; }
+    ctx->live_handles += 1;
     *out = b;
     return 0;
 }
@@ -759,7 +772,7 @@ int32_t twtml_batch_from_dense(twtml_ctx* ctx, int64_t n, int64_t d, const doubl
             });
         }
         if (!rc && cudaStreamSynchronize(ctx->stream) != cudaSuccess) rc = fail(TWTML_E_CUDA, "upload failed: %s", cudaGetErrorString(cudaGetLastError()));
-        if (rc) { cudaFree(b->X); delete b; return rc; }
+        if (rc) { cudaFree(b->X); ctx->live_handles -= 1; delete b; return rc; }
     }
     *out = b;
     return 0;
@@ -779,7 +792,7 @@ int32_t twtml_batch_synth_dense(twtml_ctx* ctx, int64_t n, int64_t d, uint64_t s
         k_synth_dense_y<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(b->X, b->ldx, (int)d, seed, row0, inv, n);
         cudaError_t e = cudaGetLastError();
         if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-        if (e != cudaSuccess) { cudaFree(b->X); delete b; return fail(TWTML_E_CUDA, "synthetic generator: %s", cudaGetErrorString(e)); }
+        if (e != cudaSuccess) { cudaFree(b->X); ctx->live_handles -= 1; delete b; return fail(TWTML_E_CUDA, "synthetic generator: %s", cudaGetErrorString(e)); }
     }
     *out = b;
     return 0;
@@ -822,24 +835,8 @@ int32_t twtml_batch_export_dense(const twtml_batch* b, double* X, double* labels
 int32_t twtml_batch_free(twtml_batch* b)
 {
     if (!b) return 0;
-    {
-        Guard g(b->ctx);
-        cudaStreamSynchronize(b->ctx->stream);
-        cudaFree(b->X);
-        cudaFree(b->rowptr);
-        cudaFree(b->colidx);
-        cudaFree(b->vals);
-        cudaFree(b->labels);
-        cudaFree(b->colptr);
-        cudaFree(b->rowidx);
-        cudaFree(b->cvals);
-        cudaFree(b->taskptr);
-        cudaFree(b->task_col);
-        cudaFree(b->task_beg);
-        cudaFree(b->task_part);
-        cudaFree(b->diff);
-    }
-    delete b;
+    Guard g(b->ctx);
+    batch_free_locked(b);
     return 0;
 }
 

@@ -31,6 +31,7 @@ static int dev_alloc(T** p, size_t count)
 static int exclusive_sum(twtml_ctx* ctx, const long long* in, long long* out, long long n)
 {
     size_t tmp = 0;
+    cudaGetLastError(); // CUB reports any error still pending in the runtime as its own
     TW_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp, in, out, n, ctx->stream));
     TW_TRY(ctx->gather.reserve(tmp));
     TW_CUDA(cub::DeviceScan::ExclusiveSum(ctx->gather.p, tmp, in, out, n, ctx->stream));
@@ -64,6 +65,7 @@ static int csr_finalize(twtml_ctx* ctx, twtml_batch* b)
             int bits = 1;
             while (((long long)1 << bits) < d) ++bits;
             size_t tmp = 0;
+            cudaGetLastError();
             cudaError_t e = cub::DeviceRadixSort::SortPairs(nullptr, tmp, b->colidx, keys_out, iota, perm, (int)nnz, 0, bits, ctx->stream);
             if (e != cudaSuccess) { rc = fail(TWTML_E_CUDA, "radix sort sizing: %s", cudaGetErrorString(e)); break; }
             if ((rc = ctx->tmp_a.reserve(tmp))) break;
@@ -109,11 +111,12 @@ static int new_csr(twtml_ctx* ctx, int64_t n, int64_t d, int64_t nnz, twtml_batc
     b->n = n;
     b->d = d;
     b->nnz = nnz;
+    ctx->live_handles += 1; // released by twtml_batch_free, also on the failure paths below and in the callers
     int rc = dev_alloc(&b->rowptr, (size_t)n + 1);
     if (!rc) rc = dev_alloc(&b->colidx, (size_t)nnz);
     if (!rc) rc = dev_alloc(&b->vals, (size_t)nnz);
     if (!rc) rc = dev_alloc(&b->labels, (size_t)n);
-    if (rc) { twtml_batch_free(b); return rc; }
+    if (rc) { batch_free_locked(b); return rc; }
     *out = b;
     return 0;
 }
@@ -210,7 +213,7 @@ int32_t twtml_batch_from_csr(twtml_ctx* ctx, int64_t n, int64_t d, const int64_t
     if (!rc && nnz) rc = upload_plain(ctx, b->vals, vals, sizeof(double) * (size_t)nnz);
     if (!rc && n) rc = upload_plain(ctx, b->labels, labels, sizeof(double) * (size_t)n);
     if (!rc) rc = csr_finalize(ctx, b);
-    if (rc) { twtml_batch_free(b); return rc; }
+    if (rc) { batch_free_locked(b); return rc; }
     *out = b;
     return 0;
 }
@@ -240,7 +243,7 @@ int32_t twtml_batch_synth_csr(twtml_ctx* ctx, int64_t n, int32_t d_text, uint64_
     cudaStreamSynchronize(ctx->stream);
     cudaFree(rowptr);
     if (!rc) rc = csr_finalize(ctx, b);
-    if (rc) { twtml_batch_free(b); return rc; }
+    if (rc) { batch_free_locked(b); return rc; }
     *out = b;
     return 0;
 }
@@ -263,7 +266,7 @@ int32_t twtml_batch_from_tweets(twtml_ctx* ctx, const uint16_t* text_utf16, cons
         TW_TRY(new_csr(ctx, 0, (int64_t)F + 4, 0, &b));
         TW_CUDA(cudaMemsetAsync(b->rowptr, 0, sizeof(long long), ctx->stream));
         int rc = csr_finalize(ctx, b);
-        if (rc) { twtml_batch_free(b); return rc; }
+        if (rc) { batch_free_locked(b); return rc; }
         *out = b;
         return 0;
     }
@@ -332,7 +335,7 @@ int32_t twtml_batch_from_tweets(twtml_ctx* ctx, const uint16_t* text_utf16, cons
 #undef TW_DO
     int rc = e == cudaSuccess ? 0 : fail(TWTML_E_CUDA, "featuriser pack failed: %s", cudaGetErrorString(e));
     if (!rc) rc = csr_finalize(ctx, b);
-    if (rc) { twtml_batch_free(b); return rc; }
+    if (rc) { batch_free_locked(b); return rc; }
     *out = b;
     return 0;
 }
