@@ -192,6 +192,18 @@ int32_t twtml_predict(const twtml_model* m, const twtml_batch* b, double* out_pr
 int32_t twtml_predict_stats(const twtml_model* m, const twtml_batch* b, double* out_real,
                             double* out_pred_rounded, twtml_stats* out);
 
+/* The statistics of twtml_predict_stats (no per-row arrays) for callers that must not allocate GPU
+ * memory.  NO COUNTERPART IN THE REFERENCE: it exists for hosts that have given the whole GPU to
+ * their own memory pool, or that cannot afford the device-wide stall a cudaMalloc / cudaFree can
+ * cause in the middle of a batch interval.  twtml_predict_stats grows per-context scratch with
+ * cudaMalloc on demand; this call uses one fixed array compiled into the library (about 1 MiB,
+ * resident on every GPU that loads it) and allocates nothing.  Limits: dense batches on a
+ * single-GPU context with at most 16384 row blocks (about 8.4 million rows); anything larger is
+ * refused with TWTML_E_INVALID_ARG.  All calls on one device share that array: calls whose GPU work
+ * overlaps (two contexts, two threads) race and must be serialised by the caller.  The first call on
+ * a device looks up the array's address; make it before starting any stream capture there. */
+int32_t twtml_predict_stats_static(const twtml_model* m, const twtml_batch* b, twtml_stats* out);
+
 /* One trainOn step (LinearRegression.scala:86 -> StreamingLinearAlgorithm.trainOn ->
  * GeneralizedLinearAlgorithm.run -> GradientDescent.runMiniBatchSGD [U]) on one micro-batch;
  * the model's weights are replaced by the result.  An empty batch leaves them untouched.

@@ -13,7 +13,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO_PATH = os.path.join(HERE, "libtwtml.so")
 HEADER = os.path.join(os.path.dirname(HERE), "include", "twtml.h")
-SOURCES = ["twtml.cu", "twtml_sparse.cu"]
+SOURCES = ["twtml.cu", "twtml_sparse.cu", "twtml_noalloc.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC,-fvisibility=hidden", "-shared"]
 
@@ -103,6 +103,7 @@ SIGNATURES = {
     "twtml_batch_free": [_vp],
     "twtml_predict": [_vp, _vp, _vp],
     "twtml_predict_stats": [_vp, _vp, _vp, _vp, C.POINTER(Stats)],
+    "twtml_predict_stats_static": [_vp, _vp, C.POINTER(Stats)],
     "twtml_train_on_batch": [_vp, _vp, _vp, _i32, C.POINTER(_i32)],
     "twtml_step": [_vp, _vp, _vp, _vp, C.POINTER(Stats), _vp, _i32, C.POINTER(_i32)],
 }

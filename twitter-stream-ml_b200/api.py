@@ -391,6 +391,16 @@ class StreamingLinearRegressionWithSGD:
             raise ArithmeticError("NumberFormatException: Utils.round on a non-finite prediction")  # Utils.scala:4-5
         return self.lastStats, (real[:b.n] if want_arrays else None), (pred[:b.n] if want_arrays else None)
 
+    def predictStatsStatic(self, rdd):
+        """The statistics of predictStats, computed without allocating GPU memory (fixed scratch inside
+        the library; dense single-GPU batches of at most ~8.4 million rows).  For hosts whose own pool owns
+        the GPU, or that cannot take a cudaMalloc stall inside a batch interval."""
+        self._require("prediction")
+        b = self._as_batch(rdd)
+        st = _lib.Stats()
+        check(_lib.lib().twtml_predict_stats_static(self._m, b._h, C.byref(st)))
+        return st.as_dict()
+
     def step(self, rdd, want_arrays=True):
         """Both output ops of one interval in one pass: stats with the pre-training weights, then train."""
         self._require("training")
