@@ -144,6 +144,22 @@ def sgd(y, d, w0, X=None, csr=None, step_size=0.1, num_iterations=50, mini_batch
     return w, hist[:it.value].copy()
 
 
+def sgd_synth(n, d, w0, seed=42, row0=0, step_size=0.1, num_iterations=3, convergence_tol=0.0, threads=None):
+    """runMiniBatchSGD over the synthetic dense batch (seed, row0), rows regenerated on the fly."""
+    threads = threads or max_threads()
+    w = np.array(w0, np.float64).copy()
+    hist = np.zeros(max(num_iterations, 1), np.float64)
+    it = C.c_int32(0)
+    L = lib()
+    L.twtml_oracle_sgd_synth.restype = C.c_int32
+    rc = L.twtml_oracle_sgd_synth(C.c_int64(n), C.c_int64(d), C.c_uint64(seed), C.c_int64(row0), _p(w),
+                                  C.c_double(step_size), C.c_int32(num_iterations), C.c_double(convergence_tol),
+                                  C.c_int32(threads * 4), C.c_int32(threads), _p(hist), C.byref(it))
+    if rc != 0:
+        raise ValueError("twtml_oracle_sgd_synth: bad arguments")
+    return w, hist[:it.value].copy()
+
+
 def predict_stats(y, d, w, X=None, csr=None, partitions=1):
     """-> dict(batch, mse, real_stdev, pred_stdev, *_raw, means), pred_raw[n], pred_rounded[n]."""
     y = np.ascontiguousarray(y, np.float64)

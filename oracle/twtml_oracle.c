@@ -351,16 +351,16 @@ static void tree_combine(agg_t* a, int P, int64_t d)
  * threads folding them.  row0 = global index of the first row (sampler key).
  * Returns 0, or -1 on bad arguments.
  * ---------------------------------------------------------------------------------- */
-TW_EXPORT int32_t twtml_oracle_sgd(
+static int32_t sgd_core(
     const double* X, int64_t ldx,
     const int64_t* rowptr, const int32_t* colidx, const double* vals,
     const double* y, int64_t n, int64_t d,
     double* w, double step_size, int32_t num_iterations, double mini_batch_fraction,
     double convergence_tol, double reg_param, int32_t updater_kind,
     int32_t partitions, int32_t threads, int64_t row0,
-    double* loss_history, int32_t* iters_run)
+    double* loss_history, int32_t* iters_run, int synth, uint64_t synth_seed)
 {
-    if ((X == NULL) == (rowptr == NULL) || d <= 0 || n < 0) return -1;
+    if ((!synth && (X == NULL) == (rowptr == NULL)) || d <= 0 || n < 0) return -1;
     if (iters_run) *iters_run = 0;
     if (n == 0) return 0;
     int P = partitions < 1 ? 1 : partitions;
@@ -382,10 +382,16 @@ TW_EXPORT int32_t twtml_oracle_sgd(
             a->loss = 0.0;
             a->cnt = 0;
             int64_t lo = (int64_t)p * n / P, hi = (int64_t)(p + 1) * n / P;
+            double* xrow = synth ? (double*)malloc(sizeof(double) * (size_t)d) : NULL;
             for (int64_t r = lo; r < hi; ++r) {
                 if (!twtml_oracle_sampled(i, (uint64_t)(row0 + r), mini_batch_fraction)) continue;
                 double diff;
-                if (X) {
+                if (synth) { /* the row is regenerated from its counters instead of being stored */
+                    double yr;
+                    twtml_oracle_synth_dense(1, d, synth_seed, row0 + r, xrow, d, &yr, 1);
+                    diff = dot_dense(xrow, w, d) - yr;
+                    for (int64_t j = 0; j < d; ++j) a->g[j] += diff * xrow[j];
+                } else if (X) {
                     const double* x = X + r * ldx;
                     diff = dot_dense(x, w, d) - y[r];
                     for (int64_t j = 0; j < d; ++j) a->g[j] += diff * x[j];
@@ -397,6 +403,7 @@ TW_EXPORT int32_t twtml_oracle_sgd(
                 a->loss += diff * diff / 2.0;
                 a->cnt += 1;
             }
+            free(xrow);
         }
         tree_combine(agg, P, d);
         int64_t m = agg[0].cnt;
@@ -425,6 +432,31 @@ TW_EXPORT int32_t twtml_oracle_sgd(
     free(gavg);
     free(wprev);
     return 0;
+}
+
+TW_EXPORT int32_t twtml_oracle_sgd(
+    const double* X, int64_t ldx,
+    const int64_t* rowptr, const int32_t* colidx, const double* vals,
+    const double* y, int64_t n, int64_t d,
+    double* w, double step_size, int32_t num_iterations, double mini_batch_fraction,
+    double convergence_tol, double reg_param, int32_t updater_kind,
+    int32_t partitions, int32_t threads, int64_t row0,
+    double* loss_history, int32_t* iters_run)
+{
+    return sgd_core(X, ldx, rowptr, colidx, vals, y, n, d, w, step_size, num_iterations, mini_batch_fraction,
+                    convergence_tol, reg_param, updater_kind, partitions, threads, row0, loss_history, iters_run, 0, 0);
+}
+
+/* The same on the synthetic dense micro-batch of twtml_oracle_synth_dense(seed, row0 ..), with every
+ * row regenerated on the fly: lets the 2^24 x 1004 configuration (134.75 GB) be checked on a host
+ * that could never hold it. */
+TW_EXPORT int32_t twtml_oracle_sgd_synth(
+    int64_t n, int64_t d, uint64_t seed, int64_t row0,
+    double* w, double step_size, int32_t num_iterations, double convergence_tol,
+    int32_t partitions, int32_t threads, double* loss_history, int32_t* iters_run)
+{
+    return sgd_core(NULL, 0, NULL, NULL, NULL, NULL, n, d, w, step_size, num_iterations, 1.0, convergence_tol, 0.0, 0,
+                    partitions, threads, row0, loss_history, iters_run, 1, seed);
 }
 
 /* ------------------------------------------------------------------------------------
