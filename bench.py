@@ -11,6 +11,7 @@ Workloads (BASELINE.json configs):
   dense_1m    2^20 rows/GPU x 1004 features, 20 iterations  (configs[1]; the default)
   dense_16m   2^24 rows/GPU x 1004 features, 50 iterations  (configs[2], HBM-roofline config; no e2e:
               134.75 GB does not stage through host memory)
+  csr_2m      2^21 rows/GPU, 2^20+4 columns, ~24 nnz/row CSR, 50 iterations (configs[4] per GPU)
 Multi-GPU: every rank holds the same number of rows (weak scaling); per iteration the ranks exchange
 their (gradSum, lossSum, count) shard vectors with one NCCL all-gather.
 """
@@ -28,6 +29,8 @@ sys.path.insert(0, ROOT)
 WORKLOADS = {
     "dense_1m": dict(rows=1 << 20, d=1004, iters=20, step=0.1),
     "dense_16m": dict(rows=1 << 24, d=1004, iters=50, step=0.1),
+    # configs[4] per GPU: 2^21 rows (2^24 over 8 GPUs), 2^20 hashed + 4 numeric columns, ~24 nnz/row, uniform columns
+    "csr_2m": dict(rows=1 << 21, d=(1 << 20) + 4, d_text=1 << 20, iters=50, step=0.005, csr=True),
 }
 METRIC = "sgd_row_iterations_per_s"
 UNIT = "row*iter/s"
@@ -177,7 +180,11 @@ def main():
     ctx.profile(True)
     model = (tw.StreamingLinearRegressionWithSGD(ctx=ctx).setNumIterations(iters).setStepSize(wl["step"])
              .setMiniBatchFraction(1.0).setConvergenceTol(0.0).setInitialWeights(tw.Vectors.zeros(d)))
-    batch = ctx.batch_synth_dense(n, d, seed=42, row0=rank * n)      # resident in HBM before the timed region
+    csr = bool(wl.get("csr"))
+    if csr:
+        batch = ctx.batch_synth_csr(n, wl["d_text"], seed=42, row0=rank * n)
+    else:
+        batch = ctx.batch_synth_dense(n, d, seed=42, row0=rank * n)  # resident in HBM before the timed region
 
     for _ in range(args.warmup):
         model.trainOnBatch(batch)
@@ -207,20 +214,34 @@ def main():
 
     # ---- end to end through the C ABI with HOST buffers: ingest (H2D) + stats + train + results (D2H)
     e2e = None
-    if (args.workload == "dense_1m" or args.rows) and args.e2e_steps > 0:
-        Xh, yh = batch.export_dense()                                   # host copy of this rank's rows
-        Xp = torch.from_numpy(Xh).pin_memory().numpy()
-        del Xh
+    if (args.workload != "dense_16m" or args.rows) and args.e2e_steps > 0:
+        if csr:
+            host = batch.export_csr()                                  # host copy of this rank's rows
+            h2d = sum(a.nbytes for a in host)
+            make = lambda: ctx.batch_from_csr(n, d, *host)
+        else:
+            Xh, yh = batch.export_dense()
+            Xp = torch.from_numpy(Xh).pin_memory().numpy()
+            del Xh
+            h2d = n * (d + 1) * 8
+            make = lambda: ctx.batch_from_dense(Xp, yh)
         model.setInitialWeights(tw.Vectors.zeros(d))
+        t_ingest = t_step = 0.0
 
         def one():
-            b = ctx.batch_from_dense(Xp, yh)
+            nonlocal t_ingest, t_step
+            t0 = time.perf_counter()
+            b = make()
+            t1 = time.perf_counter()
             st, _, _ = model.step(b, want_arrays=False)
             w = model.latestModel().weights.toArray()
+            t_ingest += t1 - t0
+            t_step += time.perf_counter() - t1
             b.free()
             return st, w
 
         one()
+        t_ingest = t_step = 0.0
         barrier()
         t0 = time.perf_counter()
         for _ in range(args.e2e_steps):
@@ -228,10 +249,13 @@ def main():
         barrier()
         e2e_s = max_over_ranks(time.perf_counter() - t0)
         e2e = {"value": world * n * iters * args.e2e_steps / e2e_s, "unit": UNIT,
-               "h2d_bytes_per_step": int(world * n * (d + 1) * 8),
+               "h2d_bytes_per_step": int(world * h2d),
                "d2h_bytes_per_step": int(world * (d * 8 + iters * 8 + 80)),
-               "steps": args.e2e_steps, "includes": "pinned host -> HBM ingest, stats + %d iterations, weights/loss/stats back" % iters}
-        del Xp
+               "steps": args.e2e_steps, "ingest_ms_per_step": t_ingest / args.e2e_steps * 1e3,
+               "compute_ms_per_step": t_step / args.e2e_steps * 1e3,
+               "ingest_GBps": h2d / max(t_ingest / args.e2e_steps, 1e-9) / 1e9,
+               "includes": "host buffers -> HBM ingest (H2D%s), stats + %d iterations, weights/loss/stats back"
+                           % (" + transpose build" if csr else ", pinned", iters)}
 
     if rank == 0:
         peak, peak_src = measured_peak()
@@ -249,11 +273,12 @@ def main():
                 "dtype": "f64", "data": "synthetic",
                 "config": {"workload": args.workload, "rows_per_gpu": n, "features": d, "sgd_iterations": iters,
                            "convergence_tol": 0.0, "parallelism": "rows sharded x%d, NCCL all-gather of shard partials per iteration" % world,
-                           "l2": "inputs (%.1f GB/GPU) larger than L2; no flush needed" % (n * (d + 2) * 8 / 1e9),
+                           "l2": "inputs (%.2f GB/GPU) larger than L2; no flush needed" % ((batch.nnz * 12 * 2 + n * 24) / 1e9 if csr else n * (d + 2) * 8 / 1e9),
                            "timing": "CUDA events on the library stream around each step's iteration loop, max over ranks"},
                 "wall_ms_per_step": wall_ms / args.steps,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": traffic, "peak_source": peak_src, "kernel": "k_dense_iter<1,TRAIN>",
+                             "traffic": traffic, "peak_source": peak_src,
+                             "kernel": "k_csr_rows + k_csr_cols + k_csr_fold (one read of the CSR credited)" if csr else "k_dense_iter<1,TRAIN,RL1>",
                              "kernel_ms": kern_ms_per_launch, "bytes_per_launch": int(kbytes),
                              "frac_of_nominal_8TBs": achieved / 8000.0},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": launches}

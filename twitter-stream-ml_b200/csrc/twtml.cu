@@ -335,7 +335,12 @@ static int reserve_scratch(twtml_ctx* ctx, const twtml_model* m, const twtml_bat
 }
 
 // block partials -> shard vectors -> (all-gather) ; leaves every rank with all shard vectors
-static int reduce_partials(twtml_ctx* ctx, const twtml_batch* b, bool gated)
+static int exchange_shards(twtml_ctx* ctx, const twtml_batch* b)
+{
+    return allgather_inplace(ctx, ctx->shards.as<double>(), (size_t)b->plan.spr * partial_width(b), ncclDouble, sizeof(double));
+}
+
+static int reduce_local(twtml_ctx* ctx, const twtml_batch* b, bool gated)
 {
     const int pv = partial_width(b), spr = b->plan.spr;
     const TrainState* gate = gated ? ctx->state.as<TrainState>() : nullptr;
@@ -348,7 +353,7 @@ static int reduce_partials(twtml_ctx* ctx, const twtml_batch* b, bool gated)
         TW_CUDA(cudaGetLastError());
         ctx->prof.other_launches += 1;
     }
-    return allgather_inplace(ctx, ctx->shards.as<double>(), (size_t)spr * pv, ncclDouble, sizeof(double));
+    return 0;
 }
 
 static int reduce_stats(twtml_ctx* ctx, const twtml_batch* b)
@@ -445,9 +450,12 @@ static int do_train(twtml_model* m, const twtml_batch* b, bool with_stats, doubl
         const int mode = (i == 1 && with_stats) ? MODE_TRAIN_STATS : MODE_TRAIN;
         if (prof) TW_CUDA(cudaEventRecord(prof_event(ctx, ne++), ctx->stream));
         TW_TRY(run_pass(ctx, m, b, mode, dp, dr, 0));
-        if (prof) TW_CUDA(cudaEventRecord(prof_event(ctx, ne++), ctx->stream));
+        // dense: the timed "iteration kernel" is k_dense_iter alone; CSR: row pass + column pass + fold
+        if (prof && !b->csr) TW_CUDA(cudaEventRecord(prof_event(ctx, ne++), ctx->stream));
         ctx->prof.iter_launches += 1;
-        TW_TRY(reduce_partials(ctx, b, true));
+        TW_TRY(reduce_local(ctx, b, true));
+        if (prof && b->csr) TW_CUDA(cudaEventRecord(prof_event(ctx, ne++), ctx->stream));
+        TW_TRY(exchange_shards(ctx, b));
         k_update<<<1, 1024, 0, ctx->stream>>>(ua);
         TW_CUDA(cudaGetLastError());
         ctx->prof.other_launches += 1;
