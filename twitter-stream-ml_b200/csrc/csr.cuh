@@ -7,10 +7,15 @@
 // would make the sums depend on the order the hardware happened to serve them, so instead the
 // batch keeps its transpose (CSC, built once at ingest, entries of a column in row order) and every
 // iteration runs
-//   k_csr_rows   rows -> diff[r] (+ lossSum, count, statistics per row block, fixed order)
-//   k_csr_cols   column tasks (<= kSeg entries of one column): sum diff[row] * value, fixed order
-//   k_csr_fold   per column: add its tasks' sums in task order -> gradSum[j]
-// Cost: the values are read twice per iteration (12 B/nnz in each form); see DESIGN.md.
+//   k_csr_rows      rows -> diff[r] (+ lossSum, count, statistics per row block, fixed order)
+//   k_csc_windows   one warp per window of 256 consecutive CSC entries: products diff[row] * value,
+//                   segmented inclusive scan keyed by the column-head bit mask; columns that lie
+//                   inside the window are written to gradSum directly, the pieces of a column that
+//                   crosses a window edge go to two per-window slots
+//   k_csc_edges     one warp per window that ends such a column: adds its pieces in window order
+// Work is balanced by entries, not by columns, so heavily skewed columns (char-bigram hashes) cost
+// the same as uniform ones.  Cost: the values are read twice per iteration (12 B/nnz in each
+// form); see DESIGN.md.
 #pragma once
 #include "common.cuh"
 #include "dense.cuh" // IterMode
@@ -19,7 +24,7 @@ namespace twtml {
 
 constexpr int kCsrThreads = 256;
 constexpr int kCsrGroups = kCsrThreads / 8; // 8 lanes per row
-constexpr int kSeg = 1024;                  // entries per column task
+constexpr int kWin = 256;                   // CSC entries per window (8 head-mask words)
 
 struct CsrIterArgs {
     const long long* rowptr;
@@ -58,15 +63,52 @@ __global__ void __launch_bounds__(kCsrThreads) k_csr_rows(const CsrIterArgs a)
         double my_loss = 0.0, my_cnt = 0.0;
         Stat7 my_stat;
         stat_zero(my_stat);
-        for (int r0 = 0; r0 < nrows; r0 += kCsrGroups) {
-            const int r = r0 + grp;
-            const bool valid = r < nrows;
-            const long long row = row0 + r;
-            double acc = 0.0;
-            if (valid) {
-                const long long b = a.rowptr[row], e = a.rowptr[row + 1];
-                for (long long k = b + l8; k < e; k += 8) acc = fma(a.vals[k], a.w[a.colidx[k]], acc);
+        // two rows per 8-lane group and two entries per lane in flight: the loads of a row's entries
+        // are issued before the dependent gathers of w, four gathers outstanding per lane
+        for (int r0 = 0; r0 < nrows; r0 += 2 * kCsrGroups) {
+          double accs[2];
+          bool valids[2];
+#pragma unroll
+          for (int h = 0; h < 2; ++h) { valids[h] = r0 + h * kCsrGroups + grp < nrows; accs[h] = 0.0; }
+          {
+            long long k[2], e[2];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const long long row = row0 + r0 + h * kCsrGroups + grp;
+                k[h] = valids[h] ? a.rowptr[row] + l8 : 0;
+                e[h] = valids[h] ? a.rowptr[row + 1] : 0;
             }
+            while (k[0] < e[0] || k[1] < e[1]) {
+                int ci[2][2];
+                double vv[2][2];
+#pragma unroll
+                for (int h = 0; h < 2; ++h)
+#pragma unroll
+                    for (int u = 0; u < 2; ++u) {
+                        const long long kk = k[h] + 8 * u;
+                        const bool p = kk < e[h];
+                        ci[h][u] = p ? a.colidx[kk] : 0;
+                        vv[h][u] = p ? a.vals[kk] : 0.0;
+                    }
+                double ww[2][2];
+#pragma unroll
+                for (int h = 0; h < 2; ++h)
+#pragma unroll
+                    for (int u = 0; u < 2; ++u) ww[h][u] = a.w[ci[h][u]];
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    accs[h] = fma(vv[h][0], ww[h][0], accs[h]); // entries k, k+8, k+16, ... in this order per lane
+                    accs[h] = fma(vv[h][1], ww[h][1], accs[h]);
+                    k[h] += 16;
+                }
+            }
+          }
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const int r = r0 + h * kCsrGroups + grp;
+            const bool valid = valids[h];
+            const long long row = row0 + r;
+            double acc = accs[h];
             acc += shfl_xor_f64(acc, 4);
             acc += shfl_xor_f64(acc, 2);
             acc += shfl_xor_f64(acc, 1);
@@ -91,6 +133,7 @@ __global__ void __launch_bounds__(kCsrThreads) k_csr_rows(const CsrIterArgs a)
                     a.out_pred[row] = acc + 0.0;
                 }
             }
+          }
         }
         if (kTrain) {
             if (l8 == 0) { sred[2 * grp] = my_loss; sred[2 * grp + 1] = my_cnt; }
@@ -121,42 +164,94 @@ __global__ void __launch_bounds__(kCsrThreads) k_csr_rows(const CsrIterArgs a)
     }
 }
 
-// one warp per column task
-static __global__ void __launch_bounds__(256) k_csr_cols(const int* __restrict__ rowidx, const double* __restrict__ cvals,
-                                                  const long long* __restrict__ colptr, const int* __restrict__ task_col,
-                                                  const long long* __restrict__ task_beg, long long ntasks,
-                                                  const double* __restrict__ diff, double* __restrict__ task_part,
-                                                  const TrainState* gate)
+// The transpose and its window index (built once per batch, csc_build in twtml_sparse.cu):
+//   rowidx / cvals   entries sorted by (column, row)
+//   headbits         bit e = entry e is the first of its column; bit nnz is set too (a virtual head
+//                    that closes the last column); zero words pad the array to (nwin + 1) * 8
+//   nzcol            the non-empty columns in order; win_first_nz[w] = heads before window w
+//   wkey[w]          column of the window's first entry; colptr as usual
+struct CscView {
+    const int* rowidx;
+    const double* cvals;
+    const unsigned* headbits;
+    const int* nzcol;
+    const long long* win_first_nz;
+    const int* wkey;
+    const long long* colptr;
+    long long nnz, nwin;
+};
+
+static __global__ void __launch_bounds__(256) k_csc_windows(const CscView c, const double* __restrict__ diff, double* __restrict__ g,
+                                                            double* __restrict__ first_part, double* __restrict__ last_part,
+                                                            const TrainState* gate)
 {
     if (gate && gate->done) return;
     const int lane = threadIdx.x & 31;
     const long long warp0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
-    for (long long tsk = warp0; tsk < ntasks; tsk += nwarps) {
-        const long long beg = task_beg[tsk];
-        const long long cend = colptr[task_col[tsk] + 1];
-        const long long end = beg + kSeg < cend ? beg + kSeg : cend;
-        double acc = 0.0;
-        for (long long e = beg + lane; e < end; e += 32) acc = fma(diff[rowidx[e]], cvals[e], acc);
-        for (int m = 16; m >= 1; m >>= 1) acc += shfl_xor_f64(acc, m);
-        if (lane == 0) task_part[tsk] = acc;
+    const unsigned le = lane == 31 ? 0xffffffffu : ((2u << lane) - 1u); // bits 0..lane
+    for (long long w = warp0; w < c.nwin; w += nwarps) {
+        const long long base = w * kWin;
+        const unsigned myword = lane < 9 ? c.headbits[w * 8 + lane] : 0u; // this window's 8 words + the next one's first
+        const long long colbase = c.win_first_nz[w];
+        int heads_before = 0;
+        double carry = 0.0;      // running sum of the segment left open by the previous round
+        bool carry_head = false; // ... and whether that segment's head lies in this window
+        unsigned hnext = 0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const unsigned hm = __shfl_sync(0xffffffffu, myword, i);
+            hnext = __shfl_sync(0xffffffffu, myword, i + 1);
+            const long long e = base + i * 32 + lane;
+            double v = 0.0;
+            if (e < c.nnz) v = diff[c.rowidx[e]] * c.cvals[e];
+            const unsigned hb = hm & le;
+            const int seg_start = hb ? 31 - __clz(hb) : -1;
+#pragma unroll
+            for (int dl = 1; dl < 32; dl <<= 1) { // segmented inclusive scan: a fixed summation tree
+                const double up = __shfl_up_sync(0xffffffffu, v, dl);
+                if (lane >= dl && lane - dl >= seg_start) v += up;
+            }
+            if (seg_start < 0) v += carry;
+            const bool next_is_head = lane < 31 ? ((hm >> (lane + 1)) & 1u) : (hnext & 1u);
+            if (e < c.nnz && next_is_head) { // this entry closes its column's run
+                if (seg_start >= 0 || carry_head) g[c.nzcol[colbase + heads_before + __popc(hb) - 1]] = v;
+                else first_part[w] = v; // the run came in from an earlier window and ends here
+            }
+            const double v31 = __shfl_sync(0xffffffffu, v, 31);
+            if (hnext & 1u) { carry = 0.0; carry_head = false; }
+            else { carry = v31; carry_head = carry_head || hm != 0u; }
+            heads_before += __popc(hm);
+        }
+        if (lane == 0 && !(hnext & 1u)) { // a run leaves through the window's end
+            if (carry_head) last_part[w] = carry;
+            else first_part[w] = carry; // the whole window is the middle of one long column
+        }
     }
 }
 
-// one warp per column: gradSum[j] = sum of its tasks in task order (0 for an empty column)
-static __global__ void __launch_bounds__(256) k_csr_fold(const long long* __restrict__ taskptr, const double* __restrict__ task_part,
-                                                  int d, double* __restrict__ g, const TrainState* gate)
+// One warp per window: if a column that came in from an earlier window ends here, add its pieces
+// (the tail piece of its first window, then the through / head pieces in window order).
+static __global__ void __launch_bounds__(256) k_csc_edges(const CscView c, const double* __restrict__ first_part,
+                                                          const double* __restrict__ last_part, double* __restrict__ g,
+                                                          const TrainState* gate)
 {
     if (gate && gate->done) return;
     const int lane = threadIdx.x & 31;
     const long long warp0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
-    for (long long j = warp0; j < d; j += nwarps) {
-        const long long b = taskptr[j], e = taskptr[j + 1];
+    for (long long w = warp0 + 1; w < c.nwin; w += nwarps) {
+        const unsigned word = lane < 9 ? c.headbits[w * 8 + lane] : 0u;
+        const unsigned first = __shfl_sync(0xffffffffu, word, 0), next = __shfl_sync(0xffffffffu, word, 8);
+        if (first & 1u) continue; // the window starts with a fresh column
+        const unsigned any = __ballot_sync(0xffffffffu, lane < 8 && word != 0u);
+        if (!any && !(next & 1u)) continue; // the column runs on into the next window
+        const int col = c.wkey[w];
+        const long long wa = c.colptr[col] / kWin; // window of the column's first entry
         double acc = 0.0;
-        for (long long k = b + lane; k < e; k += 32) acc += task_part[k];
+        for (long long u = wa + 1 + lane; u <= w; u += 32) acc += first_part[u];
         for (int m = 16; m >= 1; m >>= 1) acc += shfl_xor_f64(acc, m);
-        if (lane == 0) g[j] = acc;
+        if (lane == 0) g[col] = last_part[wa] + acc;
     }
 }
 
@@ -179,7 +274,7 @@ static __global__ void k_colptr(const int* __restrict__ keys, long long nnz, int
 
 // perm -> (row of the entry by binary search in rowptr, value)
 static __global__ void k_csc_gather(const int* __restrict__ perm, const long long* __restrict__ rowptr, long long n,
-                             const double* __restrict__ vals, long long nnz, int* __restrict__ rowidx, double* __restrict__ cvals)
+                                    const double* __restrict__ vals, long long nnz, int* __restrict__ rowidx, double* __restrict__ cvals)
 {
     const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= nnz) return;
@@ -193,20 +288,42 @@ static __global__ void k_csc_gather(const int* __restrict__ perm, const long lon
     cvals[e] = vals[src];
 }
 
-static __global__ void k_task_count(const long long* __restrict__ colptr, int d, long long* __restrict__ ntasks)
+// head bit of every entry (and the virtual head at e == nnz), one 32-bit word per warp
+static __global__ void k_csc_headbits(const int* __restrict__ keys, long long nnz, unsigned* __restrict__ headbits)
 {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j < d) ntasks[j] = (colptr[j + 1] - colptr[j] + kSeg - 1) / kSeg;
-    if (j == d) ntasks[j] = 0;
+    const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool head = e <= nnz && (e == 0 || e == nnz || keys[e] != keys[e - 1]);
+    const unsigned m = __ballot_sync(0xffffffffu, head);
+    if ((threadIdx.x & 31) == 0 && e <= nnz) headbits[e >> 5] = m;
 }
 
-static __global__ void k_task_fill(const long long* __restrict__ colptr, const long long* __restrict__ taskptr, int d,
-                            int* __restrict__ task_col, long long* __restrict__ task_beg)
+// per window: number of real heads (the virtual one at nnz excluded), and the key of its first entry
+static __global__ void k_csc_winmeta(const unsigned* __restrict__ headbits, const int* __restrict__ keys, long long nnz, long long nwin,
+                                     long long* __restrict__ winheads, int* __restrict__ wkey)
 {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= d) return;
-    long long t = taskptr[j];
-    for (long long b = colptr[j]; b < colptr[j + 1]; b += kSeg, ++t) { task_col[t] = j; task_beg[t] = b; }
+    const long long w = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (w > nwin) return;
+    if (w == nwin) { winheads[w] = 0; return; }
+    int cnt = 0;
+    for (int i = 0; i < 8; ++i) cnt += __popc(headbits[w * 8 + i]);
+    const long long lo = w * kWin, hi = lo + kWin;
+    if (nnz >= lo && nnz < hi) cnt -= 1; // the virtual head sits in this window
+    winheads[w] = cnt;
+    wkey[w] = lo < nnz ? keys[lo] : 0;
+}
+
+static __global__ void k_csc_nzcol(const int* __restrict__ keys, const unsigned* __restrict__ headbits,
+                                   const long long* __restrict__ win_first_nz, long long nnz, int* __restrict__ nzcol)
+{
+    const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= nnz) return;
+    const unsigned word = headbits[e >> 5];
+    const int bit = (int)(e & 31);
+    if (!((word >> bit) & 1u)) return;
+    const long long w = e / kWin;
+    int before = __popc(word & ((1u << bit) - 1u));
+    for (long long i = w * 8; i < (e >> 5); ++i) before += __popc(headbits[i]);
+    nzcol[win_first_nz[w] + before] = keys[e];
 }
 
 } // namespace twtml

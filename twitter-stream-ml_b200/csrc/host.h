@@ -49,7 +49,7 @@ struct twtml_ctx {
     std::mutex mu;
     int live_handles = 0; // models + batches created on this context and not yet freed
     // scratch, reused across calls
-    twtml::DevBuf partials, shards, stat_partials, stat_shards, state, loss_hist, out10, tmp_a, tmp_b, gather, lower;
+    twtml::DevBuf partials, shards, stat_partials, stat_shards, state, loss_hist, out10, tmp_a, tmp_b, gather, lower, upd_parts;
     // pinned staging ring for host -> device ingest
     void* pin[2] = {nullptr, nullptr};
     size_t pin_bytes = 0;
@@ -86,11 +86,13 @@ struct twtml_batch {
     long long* colptr = nullptr;
     int* rowidx = nullptr;
     double* cvals = nullptr;
-    long long* taskptr = nullptr;  // column -> its tasks (runs of <= kSeg entries)
-    int* task_col = nullptr;
-    long long* task_beg = nullptr;
-    double* task_part = nullptr;
-    long long ntasks = 0;
+    unsigned* headbits = nullptr;  // window index of the transpose (csr.cuh CscView)
+    int* nzcol = nullptr;
+    long long* win_first_nz = nullptr;
+    int* wkey = nullptr;
+    double* win_first_part = nullptr;
+    double* win_last_part = nullptr;
+    long long nwin = 0;
     double* diff = nullptr;        // residuals of the current iteration, n
     twtml::Plan plan{};
 };

@@ -69,63 +69,114 @@ __device__ __forceinline__ double block_sum_1024(double v, double* sm32)
     return r; // identical in every thread
 }
 
-// One CTA of 1024 threads.  Updaters [U] optimization/Updater.scala: 0 Simple (the reference path),
-// 1 SquaredL2, 2 L1.  a*b+c is deliberately NOT fused here (the JVM does not fuse).
-static __global__ void __launch_bounds__(1024) k_update(const UpdateArgs a)
+// Updaters [U] optimization/Updater.scala: 0 Simple (the reference path), 1 SquaredL2, 2 L1, on one
+// column.  a*b+c is deliberately NOT fused here (the JVM does not fuse).
+__device__ __forceinline__ void update_column(const UpdateArgs& a, int j, double cnt, double this_step, double& dn2, double& wn2,
+                                              double& l1)
 {
-    __shared__ double sm32[32];
-    TrainState* st = a.state;
-    if (st->done) return;
-    const int i = st->iter;
-    double cnt = 0.0, loss = 0.0;
+    double g = 0.0;
+    for (int s = 0; s < a.nshards; ++s) g += a.shards[(long long)s * a.pv + j];
+    g = g / cnt;
+    const double wo = a.w[j];
+    double wn;
+    if (a.updater == 1) {
+        wn = __dmul_rn(wo, 1.0 - this_step * a.reg);
+        wn = __dadd_rn(wn, __dmul_rn(-this_step, g));
+    } else {
+        wn = __dadd_rn(wo, __dmul_rn(-this_step, g));
+        if (a.updater == 2) {
+            const double shr = a.reg * this_step;
+            const double m = fabs(wn) - shr;
+            const double sg = (double)((wn > 0.0) - (wn < 0.0));
+            wn = sg * (m > 0.0 ? m : 0.0);
+        }
+    }
+    a.w[j] = wn;
+    const double df = wo - wn;
+    dn2 += df * df;
+    wn2 += wn * wn;
+    l1 += fabs(wn);
+}
+
+__device__ __forceinline__ void shard_totals(const UpdateArgs& a, double& loss, double& cnt)
+{
+    loss = cnt = 0.0;
     for (int s = 0; s < a.nshards; ++s) {
         loss += a.shards[(long long)s * a.pv + a.ldx];
         cnt += a.shards[(long long)s * a.pv + a.ldx + 1];
     }
+}
+
+// loss history, regVal, GradientDescent.isConverged [U], iteration counter
+__device__ __forceinline__ void finish_iteration(const UpdateArgs& a, double loss, double cnt, double dn2, double wn2, double l1)
+{
+    TrainState* st = a.state;
+    const int i = st->iter;
+    bool converged = false;
+    if (cnt > 0.0) {
+        a.loss_hist[st->nhist] = loss / cnt + st->reg_val;
+        st->nhist += 1;
+        const double wn = sqrt(wn2);
+        st->reg_val = a.updater == 1 ? 0.5 * a.reg * wn * wn : (a.updater == 2 ? l1 * a.reg : 0.0);
+        if (i >= 2) converged = sqrt(dn2) < a.tol * fmax(wn, 1.0);
+    }
+    st->last_count = cnt;
+    st->iter = i + 1;
+    if (converged || i + 1 > a.max_iter) st->done = 1;
+}
+
+// Narrow models (the dense path): one CTA of 1024 threads does the whole update.
+static __global__ void __launch_bounds__(1024) k_update(const UpdateArgs a)
+{
+    __shared__ double sm32[32];
+    if (a.state->done) return;
+    double cnt, loss;
+    shard_totals(a, loss, cnt);
     double dn2 = 0.0, wn2 = 0.0, l1 = 0.0;
     if (cnt > 0.0) {
-        const double this_step = a.step / sqrt((double)i);
-        for (int j = threadIdx.x; j < a.d; j += blockDim.x) {
-            double g = 0.0;
-            for (int s = 0; s < a.nshards; ++s) g += a.shards[(long long)s * a.pv + j];
-            g = g / cnt;
-            const double wo = a.w[j];
-            double wn;
-            if (a.updater == 1) {
-                wn = __dmul_rn(wo, 1.0 - this_step * a.reg);
-                wn = __dadd_rn(wn, __dmul_rn(-this_step, g));
-            } else {
-                wn = __dadd_rn(wo, __dmul_rn(-this_step, g));
-                if (a.updater == 2) {
-                    const double shr = a.reg * this_step;
-                    const double m = fabs(wn) - shr;
-                    const double sg = (double)((wn > 0.0) - (wn < 0.0));
-                    wn = sg * (m > 0.0 ? m : 0.0);
-                }
-            }
-            a.w[j] = wn;
-            const double df = wo - wn;
-            dn2 += df * df;
-            wn2 += wn * wn;
-            l1 += fabs(wn);
-        }
+        const double this_step = a.step / sqrt((double)a.state->iter);
+        for (int j = threadIdx.x; j < a.d; j += blockDim.x) update_column(a, j, cnt, this_step, dn2, wn2, l1);
     }
     dn2 = block_sum_1024(dn2, sm32);
     wn2 = block_sum_1024(wn2, sm32);
     l1 = block_sum_1024(l1, sm32);
-    if (threadIdx.x == 0) {
-        bool converged = false;
-        if (cnt > 0.0) {
-            a.loss_hist[st->nhist] = loss / cnt + st->reg_val;
-            st->nhist += 1;
-            const double wn = sqrt(wn2);
-            st->reg_val = a.updater == 1 ? 0.5 * a.reg * wn * wn : (a.updater == 2 ? l1 * a.reg : 0.0);
-            if (i >= 2) converged = sqrt(dn2) < a.tol * fmax(wn, 1.0);
-        }
-        st->last_count = cnt;
-        st->iter = i + 1;
-        if (converged || i + 1 > a.max_iter) st->done = 1;
+    if (threadIdx.x == 0) finish_iteration(a, loss, cnt, dn2, wn2, l1);
+}
+
+// Wide models (hashed text, d ~ 2^20): the columns are spread over many CTAs, each leaving its three
+// norm partials; k_update_finish adds them in CTA order and advances the state.  kWideCols columns
+// per CTA, fixed, so the partial sums do not depend on the grid the launch happens to get.
+constexpr int kWideCols = 4096;
+static __global__ void __launch_bounds__(1024) k_update_wide(const UpdateArgs a, double* __restrict__ part /* gridDim.x x 3 */)
+{
+    __shared__ double sm32[32];
+    if (a.state->done) return;
+    double cnt, loss;
+    shard_totals(a, loss, cnt);
+    double dn2 = 0.0, wn2 = 0.0, l1 = 0.0;
+    if (cnt > 0.0) {
+        const double this_step = a.step / sqrt((double)a.state->iter);
+        const int lo = blockIdx.x * kWideCols, hi = min(a.d, lo + kWideCols);
+        for (int j = lo + threadIdx.x; j < hi; j += blockDim.x) update_column(a, j, cnt, this_step, dn2, wn2, l1);
     }
+    dn2 = block_sum_1024(dn2, sm32);
+    wn2 = block_sum_1024(wn2, sm32);
+    l1 = block_sum_1024(l1, sm32);
+    if (threadIdx.x == 0) { part[blockIdx.x * 3] = dn2; part[blockIdx.x * 3 + 1] = wn2; part[blockIdx.x * 3 + 2] = l1; }
+}
+
+static __global__ void __launch_bounds__(1024) k_update_finish(const UpdateArgs a, const double* __restrict__ part, int nparts)
+{
+    __shared__ double sm32[32];
+    if (a.state->done) return;
+    double cnt, loss;
+    shard_totals(a, loss, cnt);
+    double dn2 = 0.0, wn2 = 0.0, l1 = 0.0;
+    for (int p = threadIdx.x; p < nparts; p += blockDim.x) { dn2 += part[p * 3]; wn2 += part[p * 3 + 1]; l1 += part[p * 3 + 2]; }
+    dn2 = block_sum_1024(dn2, sm32);
+    wn2 = block_sum_1024(wn2, sm32);
+    l1 = block_sum_1024(l1, sm32);
+    if (threadIdx.x == 0) finish_iteration(a, loss, cnt, dn2, wn2, l1);
 }
 
 // regVal before the first iteration = updater.compute(w, 0, 0, 1, regParam)._2 [U]
@@ -134,7 +185,8 @@ static __global__ void __launch_bounds__(1024) k_train_init(TrainState* st, cons
 {
     __shared__ double sm32[32];
     double n2 = 0.0, l1 = 0.0;
-    for (int j = threadIdx.x; j < d; j += blockDim.x) { n2 += w[j] * w[j]; l1 += fabs(w[j]); }
+    if (updater != 0 && reg != 0.0)
+        for (int j = threadIdx.x; j < d; j += blockDim.x) { n2 += w[j] * w[j]; l1 += fabs(w[j]); }
     n2 = block_sum_1024(n2, sm32);
     l1 = block_sum_1024(l1, sm32);
     if (threadIdx.x == 0) {

@@ -331,6 +331,7 @@ static int reserve_scratch(twtml_ctx* ctx, const twtml_model* m, const twtml_bat
     TW_TRY(ctx->state.reserve(sizeof(TrainState)));
     TW_TRY(ctx->loss_hist.reserve(sizeof(double) * (size_t)std::max(1, m->num_iter)));
     TW_TRY(ctx->out10.reserve(sizeof(double) * 16));
+    TW_TRY(ctx->upd_parts.reserve(sizeof(double) * 3 * (size_t)((m->d + kWideCols - 1) / kWideCols)));
     return 0;
 }
 
@@ -456,9 +457,16 @@ static int do_train(twtml_model* m, const twtml_batch* b, bool with_stats, doubl
         TW_TRY(reduce_local(ctx, b, true));
         if (prof && b->csr) TW_CUDA(cudaEventRecord(prof_event(ctx, ne++), ctx->stream));
         TW_TRY(exchange_shards(ctx, b));
-        k_update<<<1, 1024, 0, ctx->stream>>>(ua);
+        if (m->d <= 2 * kWideCols) {
+            k_update<<<1, 1024, 0, ctx->stream>>>(ua);
+            ctx->prof.other_launches += 1;
+        } else {
+            const int nparts = (int)((m->d + kWideCols - 1) / kWideCols);
+            k_update_wide<<<nparts, 1024, 0, ctx->stream>>>(ua, ctx->upd_parts.as<double>());
+            k_update_finish<<<1, 1024, 0, ctx->stream>>>(ua, ctx->upd_parts.as<double>(), nparts);
+            ctx->prof.other_launches += 2;
+        }
         TW_CUDA(cudaGetLastError());
-        ctx->prof.other_launches += 1;
         if (i == 1 && with_stats) TW_TRY(reduce_stats(ctx, b));
     }
     if (prof) TW_CUDA(cudaEventRecord(prof_event(ctx, ne++), ctx->stream));
@@ -498,7 +506,8 @@ void batch_free_locked(twtml_batch* b)
 {
     cudaStreamSynchronize(b->ctx->stream);
     for (void* p : {(void*)b->X, (void*)b->rowptr, (void*)b->colidx, (void*)b->vals, (void*)b->labels, (void*)b->colptr, (void*)b->rowidx,
-                    (void*)b->cvals, (void*)b->taskptr, (void*)b->task_col, (void*)b->task_beg, (void*)b->task_part, (void*)b->diff})
+                    (void*)b->cvals, (void*)b->headbits, (void*)b->nzcol, (void*)b->win_first_nz, (void*)b->wkey, (void*)b->win_first_part,
+                    (void*)b->win_last_part, (void*)b->diff})
         cudaFree(p);
     b->ctx->live_handles -= 1;
     delete b;
@@ -591,7 +600,7 @@ int32_t twtml_destroy(twtml_ctx* ctx)
     cudaStreamSynchronize(ctx->stream);
     if (ctx->comm) nccl_api().CommDestroy(ctx->comm);
     for (DevBuf* b : {&ctx->partials, &ctx->shards, &ctx->stat_partials, &ctx->stat_shards, &ctx->state, &ctx->loss_hist, &ctx->out10,
-                      &ctx->tmp_a, &ctx->tmp_b, &ctx->gather, &ctx->lower})
+                      &ctx->tmp_a, &ctx->tmp_b, &ctx->gather, &ctx->lower, &ctx->upd_parts})
         b->release();
     for (int i = 0; i < 2; ++i) {
         if (ctx->pin[i]) cudaFreeHost(ctx->pin[i]);

@@ -49,11 +49,19 @@ static int csr_finalize(twtml_ctx* ctx, twtml_batch* b)
         return fail(TWTML_E_INVALID_ARG, "CSR batch too large for 32-bit entry indices (%lld rows, %lld nnz per GPU)", (long long)b->n, (long long)b->nnz);
     const int d = (int)b->d;
     const long long nnz = b->nnz;
+    const long long nwin = (nnz + kWin - 1) / kWin;
+    b->nwin = nwin;
     TW_TRY(dev_alloc(&b->colptr, (size_t)d + 1));
     TW_TRY(dev_alloc(&b->rowidx, (size_t)nnz));
     TW_TRY(dev_alloc(&b->cvals, (size_t)nnz));
-    TW_TRY(dev_alloc(&b->taskptr, (size_t)d + 2));
     TW_TRY(dev_alloc(&b->diff, (size_t)b->n));
+    TW_TRY(dev_alloc(&b->headbits, (size_t)(nwin + 1) * 8));
+    TW_TRY(dev_alloc(&b->win_first_nz, (size_t)nwin + 1));
+    TW_TRY(dev_alloc(&b->wkey, (size_t)nwin + 1));
+    TW_TRY(dev_alloc(&b->win_first_part, (size_t)nwin + 1));
+    TW_TRY(dev_alloc(&b->win_last_part, (size_t)nwin + 1));
+    TW_TRY(dev_alloc(&b->nzcol, (size_t)std::min<long long>(nnz, d) + 1));
+    TW_CUDA(cudaMemsetAsync(b->headbits, 0, sizeof(unsigned) * (size_t)(nwin + 1) * 8, ctx->stream));
     if (nnz > 0) {
         int *keys_out = nullptr, *iota = nullptr, *perm = nullptr;
         TW_TRY(dev_alloc(&keys_out, (size_t)nnz));
@@ -74,7 +82,20 @@ static int csr_finalize(twtml_ctx* ctx, twtml_batch* b)
             if (e != cudaSuccess) { rc = fail(TWTML_E_CUDA, "radix sort: %s", cudaGetErrorString(e)); break; }
             k_colptr<<<blocks_for(nnz + 1, 256), 256, 0, ctx->stream>>>(keys_out, nnz, d, b->colptr);
             k_csc_gather<<<blocks_for(nnz, 256), 256, 0, ctx->stream>>>(perm, b->rowptr, b->n, b->vals, nnz, b->rowidx, b->cvals);
-            if (cudaGetLastError() != cudaSuccess) rc = fail(TWTML_E_CUDA, "transpose kernels failed to launch");
+            // window index of the transpose: head bits, heads per window -> first non-empty column per window
+            k_csc_headbits<<<blocks_for(nnz + 1, 256), 256, 0, ctx->stream>>>(keys_out, nnz, b->headbits);
+            long long* winheads = reinterpret_cast<long long*>(iota); // iota is dead from here on; nnz ints >= nwin+1 int64 when nnz >= 2
+            long long* winheads_own = nullptr;
+            if ((size_t)nnz * sizeof(int) < (size_t)(nwin + 1) * sizeof(long long)) {
+                if ((rc = dev_alloc(&winheads_own, (size_t)nwin + 1))) break;
+                winheads = winheads_own;
+            }
+            k_csc_winmeta<<<blocks_for(nwin + 1, 256), 256, 0, ctx->stream>>>(b->headbits, keys_out, nnz, nwin, winheads, b->wkey);
+            rc = exclusive_sum(ctx, winheads, b->win_first_nz, nwin + 1);
+            if (!rc) k_csc_nzcol<<<blocks_for(nnz, 256), 256, 0, ctx->stream>>>(keys_out, b->headbits, b->win_first_nz, nnz, b->nzcol);
+            if (!rc && cudaGetLastError() != cudaSuccess) rc = fail(TWTML_E_CUDA, "transpose kernels failed to launch");
+            cudaStreamSynchronize(ctx->stream);
+            cudaFree(winheads_own);
         } while (0);
         cudaStreamSynchronize(ctx->stream);
         cudaFree(keys_out);
@@ -83,23 +104,8 @@ static int csr_finalize(twtml_ctx* ctx, twtml_batch* b)
         if (rc) return rc;
     } else {
         TW_CUDA(cudaMemsetAsync(b->colptr, 0, sizeof(long long) * ((size_t)d + 1), ctx->stream));
+        TW_CUDA(cudaStreamSynchronize(ctx->stream));
     }
-    long long* ntasks = nullptr;
-    TW_TRY(dev_alloc(&ntasks, (size_t)d + 2));
-    k_task_count<<<blocks_for(d + 1, 256), 256, 0, ctx->stream>>>(b->colptr, d, ntasks);
-    int rc = exclusive_sum(ctx, ntasks, b->taskptr, d + 1);
-    long long total = 0;
-    if (!rc && cudaMemcpyAsync(&total, b->taskptr + d, sizeof(total), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) rc = fail(TWTML_E_CUDA, "task count copy failed");
-    cudaStreamSynchronize(ctx->stream);
-    cudaFree(ntasks);
-    if (rc) return rc;
-    b->ntasks = total;
-    TW_TRY(dev_alloc(&b->task_col, (size_t)total));
-    TW_TRY(dev_alloc(&b->task_beg, (size_t)total));
-    TW_TRY(dev_alloc(&b->task_part, (size_t)total));
-    k_task_fill<<<blocks_for(d, 256), 256, 0, ctx->stream>>>(b->colptr, b->taskptr, d, b->task_col, b->task_beg);
-    TW_CUDA(cudaGetLastError());
-    TW_CUDA(cudaStreamSynchronize(ctx->stream));
     return 0;
 }
 
@@ -159,12 +165,14 @@ int csr_launch_iter(twtml_ctx* ctx, const twtml_model* m, const twtml_batch* b, 
 int csr_reduce(twtml_ctx* ctx, const twtml_batch* b, double* shard_out, const TrainState* gate)
 {
     const int d = (int)b->d;
-    if (b->ntasks > 0) {
-        const unsigned g1 = (unsigned)std::min<long long>((b->ntasks + 7) / 8, (long long)ctx->sm_count * 32);
-        k_csr_cols<<<g1, 256, 0, ctx->stream>>>(b->rowidx, b->cvals, b->colptr, b->task_col, b->task_beg, b->ntasks, b->diff, b->task_part, gate);
+    // columns without entries keep gradSum = 0; every other column is written exactly once below
+    TW_CUDA(cudaMemsetAsync(shard_out, 0, sizeof(double) * (size_t)d, ctx->stream));
+    if (b->nwin > 0) {
+        CscView c{b->rowidx, b->cvals, b->headbits, b->nzcol, b->win_first_nz, b->wkey, b->colptr, b->nnz, b->nwin};
+        const unsigned g1 = (unsigned)std::min<long long>((b->nwin + 7) / 8, (long long)ctx->sm_count * 32);
+        k_csc_windows<<<g1, 256, 0, ctx->stream>>>(c, b->diff, shard_out, b->win_first_part, b->win_last_part, gate);
+        k_csc_edges<<<g1, 256, 0, ctx->stream>>>(c, b->win_first_part, b->win_last_part, shard_out, gate);
     }
-    const unsigned g2 = (unsigned)std::min<long long>(((long long)d + 7) / 8, (long long)ctx->sm_count * 32);
-    k_csr_fold<<<g2, 256, 0, ctx->stream>>>(b->taskptr, b->task_part, d, shard_out, gate);
     dim3 grid(1, 1), block(32, 32);
     k_shard_reduce<<<grid, block, 0, ctx->stream>>>(ctx->partials.as<double>(), 2, b->plan, shard_out + d, gate);
     TW_CUDA(cudaGetLastError());
