@@ -237,21 +237,37 @@ static __global__ void __launch_bounds__(256) k_csc_edges(const CscView c, const
                                                           const TrainState* gate)
 {
     if (gate && gate->done) return;
+    // One thread looks at one window; a column that spans just two windows (the common case) is
+    // finished by that thread, longer spans are then folded by the whole warp, lane-strided with a
+    // fixed butterfly, one after the other.
     const int lane = threadIdx.x & 31;
-    const long long warp0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
-    for (long long w = warp0 + 1; w < c.nwin; w += nwarps) {
-        const unsigned word = lane < 9 ? c.headbits[w * 8 + lane] : 0u;
-        const unsigned first = __shfl_sync(0xffffffffu, word, 0), next = __shfl_sync(0xffffffffu, word, 8);
-        if (first & 1u) continue; // the window starts with a fresh column
-        const unsigned any = __ballot_sync(0xffffffffu, lane < 8 && word != 0u);
-        if (!any && !(next & 1u)) continue; // the column runs on into the next window
-        const int col = c.wkey[w];
-        const long long wa = c.colptr[col] / kWin; // window of the column's first entry
-        double acc = 0.0;
-        for (long long u = wa + 1 + lane; u <= w; u += 32) acc += first_part[u];
-        for (int m = 16; m >= 1; m >>= 1) acc += shfl_xor_f64(acc, m);
-        if (lane == 0) g[col] = last_part[wa] + acc;
+    const long long t0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long nt = (long long)gridDim.x * blockDim.x;
+    for (long long wbase = t0 - lane; wbase + 1 < c.nwin; wbase += nt) {
+        const long long w = wbase + lane + 1;
+        long long wa = -1; // >= 0: a column that came in from window wa ends in window w
+        int col = 0;
+        if (w < c.nwin && !(c.headbits[w * 8] & 1u)) {
+            unsigned any = 0;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) any |= c.headbits[w * 8 + i];
+            if (any || (c.headbits[w * 8 + 8] & 1u)) {
+                col = c.wkey[w];
+                wa = c.colptr[col] / kWin;
+                if (wa == w - 1) { g[col] = last_part[wa] + first_part[w]; wa = -1; }
+            }
+        }
+        unsigned todo = __ballot_sync(0xffffffffu, wa >= 0);
+        while (todo) {
+            const int src = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const long long wa_s = __shfl_sync(0xffffffffu, wa, src), w_s = wbase + src + 1;
+            const int col_s = __shfl_sync(0xffffffffu, col, src);
+            double acc = 0.0;
+            for (long long u = wa_s + 1 + lane; u <= w_s; u += 32) acc += first_part[u];
+            for (int m = 16; m >= 1; m >>= 1) acc += shfl_xor_f64(acc, m);
+            if (lane == 0) g[col_s] = last_part[wa_s] + acc;
+        }
     }
 }
 

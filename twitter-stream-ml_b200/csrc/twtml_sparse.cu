@@ -171,7 +171,8 @@ int csr_reduce(twtml_ctx* ctx, const twtml_batch* b, double* shard_out, const Tr
         CscView c{b->rowidx, b->cvals, b->headbits, b->nzcol, b->win_first_nz, b->wkey, b->colptr, b->nnz, b->nwin};
         const unsigned g1 = (unsigned)std::min<long long>((b->nwin + 7) / 8, (long long)ctx->sm_count * 32);
         k_csc_windows<<<g1, 256, 0, ctx->stream>>>(c, b->diff, shard_out, b->win_first_part, b->win_last_part, gate);
-        k_csc_edges<<<g1, 256, 0, ctx->stream>>>(c, b->win_first_part, b->win_last_part, shard_out, gate);
+        const unsigned g2 = (unsigned)std::min<long long>((b->nwin + 255) / 256, (long long)ctx->sm_count * 32);
+        k_csc_edges<<<g2, 256, 0, ctx->stream>>>(c, b->win_first_part, b->win_last_part, shard_out, gate);
     }
     dim3 grid(1, 1), block(32, 32);
     k_shard_reduce<<<grid, block, 0, ctx->stream>>>(ctx->partials.as<double>(), 2, b->plan, shard_out + d, gate);
