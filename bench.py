@@ -130,7 +130,7 @@ def main():
     ap.add_argument("--workload", default="dense_1m", choices=sorted(WORKLOADS))
     ap.add_argument("--rows", type=int, default=0, help="override rows per GPU (testing)")
     ap.add_argument("--iters", type=int, default=0, help="override SGD iterations per micro-batch (testing)")
-    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--e2e-steps", type=int, default=4)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     wl = dict(WORKLOADS[args.workload])
@@ -223,29 +223,34 @@ def main():
             Xh, yh = batch.export_dense()
             Xp = torch.from_numpy(Xh).pin_memory().numpy()
             del Xh
+            yp = torch.from_numpy(yh).pin_memory().numpy()
             h2d = n * (d + 1) * 8
-            make = lambda: ctx.batch_from_dense(Xp, yh)
+            # page-locked buffers: the library DMAs straight from them on its copy stream, so the ingest of
+            # step t+1 is issued before step t computes and overlaps it (streaming ingest)
+            make = lambda: ctx.batch_from_dense_async(Xp, yp)
         model.setInitialWeights(tw.Vectors.zeros(d))
         t_ingest = t_step = 0.0
 
-        def one():
+        def run(k):
             nonlocal t_ingest, t_step
-            t0 = time.perf_counter()
-            b = make()
-            t1 = time.perf_counter()
-            st, _, _ = model.step(b, want_arrays=False)
-            w = model.latestModel().weights.toArray()
-            t_ingest += t1 - t0
-            t_step += time.perf_counter() - t1
-            b.free()
+            nxt = make()
+            for i in range(k):
+                b = nxt
+                t0 = time.perf_counter()
+                nxt = make() if i + 1 < k else None        # every step's rows cross PCIe inside the timed region
+                t1 = time.perf_counter()
+                st, _, _ = model.step(b, want_arrays=False)
+                w = model.latestModel().weights.toArray()
+                t_ingest += t1 - t0
+                t_step += time.perf_counter() - t1
+                b.free()
             return st, w
 
-        one()
+        run(1)
         t_ingest = t_step = 0.0
         barrier()
         t0 = time.perf_counter()
-        for _ in range(args.e2e_steps):
-            st, w = one()
+        st, w = run(args.e2e_steps)
         barrier()
         e2e_s = max_over_ranks(time.perf_counter() - t0)
         e2e = {"value": world * n * iters * args.e2e_steps / e2e_s, "unit": UNIT,
@@ -253,9 +258,9 @@ def main():
                "d2h_bytes_per_step": int(world * (d * 8 + iters * 8 + 80)),
                "steps": args.e2e_steps, "ingest_ms_per_step": t_ingest / args.e2e_steps * 1e3,
                "compute_ms_per_step": t_step / args.e2e_steps * 1e3,
-               "ingest_GBps": h2d / max(t_ingest / args.e2e_steps, 1e-9) / 1e9,
+               "h2d_GBps_effective": h2d * args.e2e_steps / e2e_s / 1e9,
                "includes": "host buffers -> HBM ingest (H2D%s), stats + %d iterations, weights/loss/stats back"
-                           % (" + transpose build" if csr else ", pinned", iters)}
+                           % (" + transpose build" if csr else ", pinned, next step's copy overlapping this step's compute", iters)}
 
     if rank == 0:
         peak, peak_src = measured_peak()

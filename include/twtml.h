@@ -162,6 +162,18 @@ int32_t twtml_batch_from_csr(twtml_ctx* ctx, int64_t n, int64_t d, const int64_t
 int32_t twtml_batch_from_dense(twtml_ctx* ctx, int64_t n, int64_t d, const double* X, int64_t ld_x,
                                const double* labels, twtml_batch** out);
 
+/* The same, returning while the rows are still on their way: the copy runs on the library's copy
+ * stream and overlaps whatever the context is computing, which is how batch t+1 is ingested under
+ * the SGD of batch t (north_star: "packed once into pinned host memory and copied asynchronously";
+ * the reference's receiver likewise fills the next RDD while foreachRDD works on the current one).
+ * X and labels must be page-locked host memory and stay untouched until the batch has been used by
+ * a compute call or twtml_batch_ready(b, 1, ..) has returned; with pageable memory, or on a
+ * multi-rank context, the call simply behaves like twtml_batch_from_dense. */
+int32_t twtml_batch_from_dense_async(twtml_ctx* ctx, int64_t n, int64_t d, const double* X, int64_t ld_x,
+                                     const double* labels, twtml_batch** out);
+/* *ready = 1 once the batch's rows are in HBM; wait != 0 blocks until then. */
+int32_t twtml_batch_ready(const twtml_batch* b, int32_t wait, int32_t* ready);
+
 /* Synthetic micro-batches generated in HBM (measurement tool for SURVEY.md 8d configs 2-5; no
  * reference counterpart).  Bit-identical to oracle/twtml_oracle.c's generators for the same
  * (seed, global first row). */

@@ -227,3 +227,32 @@ def test_driver_loop_like_the_reference(tw, ctx, oracle):
     stream.push(ctx.batch_from_dense(np.zeros((0, d)), np.zeros(0)))           # empty interval: both ops skip
     assert seen[-1] is None
     assert relerr(model.latestModel().weights.toArray(), w_ref) < RTOL
+
+
+def test_async_ingest_overlaps_and_matches_sync(tw, ctx, oracle):
+    """twtml_batch_from_dense_async: page-locked rows are copied on the copy stream; the next batch can be
+    on its way while the current one trains; contents and results equal the synchronous path's."""
+    import torch
+    d = 1004
+    host = []
+    for t in range(3):
+        X, y = oracle.synth_dense(3000 + 17 * t, d, seed=400 + t)
+        host.append((torch.from_numpy(X).pin_memory().numpy(), torch.from_numpy(np.round(y * 300 + 400)).pin_memory().numpy()))
+    m_sync = make_model(tw, ctx, d, np.zeros(d), step=0.005, iters=10)
+    m_async = make_model(tw, ctx, d, np.zeros(d), step=0.005, iters=10)
+    for X, y in host:
+        m_sync.trainOnBatch(ctx.batch_from_dense(X, y))
+    nxt = ctx.batch_from_dense_async(*host[0])
+    for t in range(3):
+        b = nxt
+        nxt = ctx.batch_from_dense_async(*host[t + 1]) if t + 1 < 3 else None
+        m_async.trainOnBatch(b)
+        assert b.ready()
+        X2, y2 = b.export_dense()
+        assert np.array_equal(X2, host[t][0]) and np.array_equal(y2, host[t][1])
+        b.free()
+    assert np.array_equal(m_sync.latestModel().weights.toArray(), m_async.latestModel().weights.toArray())
+    # pageable memory quietly takes the synchronous path
+    Xp, yp = oracle.synth_dense(100, 8, seed=1)
+    b = ctx.batch_from_dense_async(Xp, yp)
+    assert b.ready(wait=True) and np.array_equal(b.export_dense()[0], Xp)

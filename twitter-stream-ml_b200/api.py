@@ -75,6 +75,20 @@ class Context:
                                                 ptr(labels), C.byref(h)))
         return Batch(self, h)
 
+    def batch_from_dense_async(self, X, labels):
+        """Like batch_from_dense, but returns while the copy runs (page-locked X / labels, C-contiguous
+        rows); the arrays are kept alive by the returned Batch until it is ready."""
+        X = np.asarray(X, np.float64)
+        labels = np.ascontiguousarray(labels, np.float64)
+        if X.ndim != 2 or X.shape[0] != labels.shape[0] or X.strides[1] != 8 or X.strides[0] % 8:
+            raise ValueError("X must be n x d float64 with unit column stride and one label per row")
+        h = C.c_void_p()
+        check(_lib.lib().twtml_batch_from_dense_async(self._h, X.shape[0], X.shape[1], ptr(X), X.strides[0] // 8 if X.shape[0] > 1 else X.shape[1],
+                                                      ptr(labels), C.byref(h)))
+        b = Batch(self, h)
+        b._keep = (X, labels)
+        return b
+
     def batch_from_csr(self, n, d, rowptr, colidx, vals, labels):
         rowptr, colidx = _lib.arr(rowptr, np.int64), _lib.arr(colidx, np.int32)
         vals, labels = _lib.arr(vals, np.float64), _lib.arr(labels, np.float64)
@@ -116,6 +130,11 @@ class Batch:
 
     def count(self):
         return self.n
+
+    def ready(self, wait=False):
+        r = C.c_int32()
+        check(_lib.lib().twtml_batch_ready(self._h, int(wait), C.byref(r)))
+        return bool(r.value)
 
     def isEmpty(self):
         return self.n == 0

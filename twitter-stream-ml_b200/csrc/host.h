@@ -45,6 +45,7 @@ struct twtml_ctx {
     int spr = twtml::kMaxShards;  // shards per rank
     int nshards = twtml::kMaxShards;
     cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr; // asynchronous ingest (twtml_batch_from_dense_async)
     ncclComm_t comm = nullptr;
     std::mutex mu;
     int live_handles = 0; // models + batches created on this context and not yet freed
@@ -75,6 +76,7 @@ struct twtml_batch {
     bool csr = false;
     int64_t n = 0, d = 0, nnz = 0;
     int64_t n_global = 0, row0_global = 0;
+    cudaEvent_t ready = nullptr; // set by asynchronous ingest: recorded on the copy stream when the rows are in HBM
     // dense
     double* X = nullptr;
     int64_t ldx = 0;

@@ -370,6 +370,13 @@ static int reduce_stats(twtml_ctx* ctx, const twtml_batch* b)
     return 0;
 }
 
+// a batch from twtml_batch_from_dense_async may still be in flight on the copy stream
+static int wait_ready(twtml_ctx* ctx, const twtml_batch* b)
+{
+    if (b->ready) TW_CUDA(cudaStreamWaitEvent(ctx->stream, b->ready, 0));
+    return 0;
+}
+
 static int check_pair(const twtml_model* m, const twtml_batch* b, const char* what)
 {
     if (!m || !b) return fail(TWTML_E_INVALID_ARG, "%s: null handle", what);
@@ -391,6 +398,7 @@ static int do_predict_stats(const twtml_model* m, const twtml_batch* b, double* 
 {
     twtml_ctx* ctx = m->ctx;
     if (b->n_global == 0) { stats_empty(out); return 0; }
+    TW_TRY(wait_ready(ctx, b));
     TW_TRY(reserve_scratch(ctx, m, b));
     double *dp = nullptr, *dr = nullptr;
     if (out_pred) { TW_TRY(ctx->tmp_a.reserve(sizeof(double) * (size_t)std::max<int64_t>(1, b->n))); dp = ctx->tmp_a.as<double>(); }
@@ -416,6 +424,7 @@ static int do_train(twtml_model* m, const twtml_batch* b, bool with_stats, doubl
         if (with_stats && out) stats_empty(out);
         return 0;
     }
+    TW_TRY(wait_ready(ctx, b));
     TW_TRY(reserve_scratch(ctx, m, b));
     double *dp = nullptr, *dr = nullptr;
     if (with_stats && out_pred) { TW_TRY(ctx->tmp_a.reserve(sizeof(double) * (size_t)std::max<int64_t>(1, b->n))); dp = ctx->tmp_a.as<double>(); }
@@ -504,6 +513,10 @@ static int do_train(twtml_model* m, const twtml_batch* b, bool with_stats, doubl
 // caller holds the context lock (or is the only owner)
 void batch_free_locked(twtml_batch* b)
 {
+    if (b->ready) {
+        cudaEventSynchronize(b->ready); // its own copy only; later batches may still be arriving
+        cudaEventDestroy(b->ready);
+    }
     cudaStreamSynchronize(b->ctx->stream);
     for (void* p : {(void*)b->X, (void*)b->rowptr, (void*)b->colidx, (void*)b->vals, (void*)b->labels, (void*)b->colptr, (void*)b->rowidx,
                     (void*)b->cvals, (void*)b->headbits, (void*)b->nzcol, (void*)b->win_first_nz, (void*)b->wkey, (void*)b->win_first_part,
@@ -556,6 +569,7 @@ static int32_t create_common(int32_t device, int32_t rank, int32_t world, const 
     c->nshards = c->spr * world;
     cudaError_t se = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
     if (se != cudaSuccess) { delete c; return fail(TWTML_E_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(se)); }
+    cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
     for (int i = 0; i < 2; ++i) cudaEventCreateWithFlags(&c->pin_ev[i], cudaEventDisableTiming);
     if (world > 1) {
         if (!nccl_api().ok) { delete c; return fail(TWTML_E_NCCL, "libnccl.so.2 could not be loaded: %s", dlerror()); }
@@ -608,6 +622,7 @@ int32_t twtml_destroy(twtml_ctx* ctx)
     }
     for (cudaEvent_t e : ctx->ev) cudaEventDestroy(e);
     cudaStreamDestroy(ctx->stream);
+    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     delete ctx;
     return 0;
 }
@@ -795,6 +810,59 @@ int32_t twtml_batch_from_dense(twtml_ctx* ctx, int64_t n, int64_t d, const doubl
     return 0;
 }
 
+static bool page_locked(const void* p)
+{
+    cudaPointerAttributes pa{};
+    const bool yes = cudaPointerGetAttributes(&pa, p) == cudaSuccess && pa.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+    return yes;
+}
+
+int32_t twtml_batch_from_dense_async(twtml_ctx* ctx, int64_t n, int64_t d, const double* X, int64_t ld_x, const double* labels, twtml_batch** out)
+{
+    if (!ctx || !out) return fail(TWTML_E_INVALID_ARG, "null argument");
+    if (n < 0 || d < 1 || (n > 0 && (!X || !labels)) || ld_x < d) return fail(TWTML_E_INVALID_ARG, "twtml_batch_from_dense_async: bad shape or null data");
+    // only page-locked host memory can be copied without a host-side staging pass, and the row-count
+    // exchange of a multi-rank context would have to wait for the compute stream: both fall back
+    if (n == 0 || ctx->world != 1 || !page_locked(X) || !page_locked(labels)) return twtml_batch_from_dense(ctx, n, d, X, ld_x, labels, out);
+    Guard g(ctx);
+    twtml_batch* b = nullptr;
+    TW_TRY(new_dense(ctx, n, d, &b));
+    cudaError_t e = cudaMalloc(&b->labels, sizeof(double) * (size_t)n);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&b->ready, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaMemcpy2DAsync(b->X, (size_t)b->ldx * 8, X, (size_t)ld_x * 8, (size_t)d * 8, (size_t)n, cudaMemcpyHostToDevice, ctx->copy_stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(b->labels, labels, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, ctx->copy_stream);
+    if (e == cudaSuccess) {
+        k_scatter_labels<<<(unsigned)((n + 255) / 256), 256, 0, ctx->copy_stream>>>(b->X, b->ldx, (int)d, b->labels, n);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaEventRecord(b->ready, ctx->copy_stream);
+    if (e != cudaSuccess) {
+        int rc = fail(e == cudaErrorMemoryAllocation ? TWTML_E_OOM : TWTML_E_CUDA, "asynchronous ingest: %s", cudaGetErrorString(e));
+        batch_free_locked(b);
+        return rc;
+    }
+    *out = b;
+    return 0;
+}
+
+int32_t twtml_batch_ready(const twtml_batch* b, int32_t wait, int32_t* ready)
+{
+    if (!b) return fail(TWTML_E_INVALID_ARG, "null batch");
+    int r = 1;
+    if (b->ready) {
+        Guard g(b->ctx);
+        if (wait) TW_CUDA(cudaEventSynchronize(b->ready));
+        else {
+            cudaError_t e = cudaEventQuery(b->ready);
+            if (e == cudaErrorNotReady) r = 0;
+            else if (e != cudaSuccess) return fail(TWTML_E_CUDA, "cudaEventQuery: %s", cudaGetErrorString(e));
+        }
+    }
+    if (ready) *ready = r;
+    return 0;
+}
+
 int32_t twtml_batch_synth_dense(twtml_ctx* ctx, int64_t n, int64_t d, uint64_t seed, int64_t row0, twtml_batch** out)
 {
     if (!ctx || !out) return fail(TWTML_E_INVALID_ARG, "null argument");
@@ -839,6 +907,7 @@ int32_t twtml_batch_export_dense(const twtml_batch* b, double* X, double* labels
     if (b->n == 0) return 0;
     twtml_ctx* ctx = b->ctx;
     Guard g(ctx);
+    TW_TRY(wait_ready(ctx, b));
     TW_TRY(ctx->tmp_a.reserve(sizeof(double) * (size_t)b->n * (size_t)b->d));
     TW_TRY(ctx->tmp_b.reserve(sizeof(double) * (size_t)b->n));
     k_gather_dense<<<(unsigned)std::min<int64_t>(b->n, 65535), 256, 0, ctx->stream>>>(b->X, b->ldx, (int)b->d, ctx->tmp_a.as<double>(), ctx->tmp_b.as<double>(), b->n);
@@ -865,6 +934,7 @@ int32_t twtml_predict(const twtml_model* m, const twtml_batch* b, double* out_pr
     twtml_ctx* ctx = m->ctx;
     Guard g(ctx);
     if (b->n == 0) return 0;
+    TW_TRY(wait_ready(ctx, b));
     TW_TRY(reserve_scratch(ctx, m, b));
     TW_TRY(ctx->tmp_a.reserve(sizeof(double) * (size_t)b->n));
     TW_TRY(run_pass(ctx, m, b, MODE_PREDICT, ctx->tmp_a.as<double>(), nullptr, 0));

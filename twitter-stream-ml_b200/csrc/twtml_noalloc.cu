@@ -95,6 +95,7 @@ extern "C" int32_t twtml_predict_stats_static(const twtml_model* m, const twtml_
         out->mse = out->real_stdev = out->pred_stdev = out->mse_raw = out->real_stdev_raw = out->pred_stdev_raw = out->real_mean = out->pred_mean = NAN;
         return 0;
     }
+    if (b->ready) TW_CUDA(cudaStreamWaitEvent(ctx->stream, b->ready, 0)); // batch still arriving (asynchronous ingest)
     double* scratch = nullptr;
     TW_TRY(setup_device(ctx->device, &scratch));
     double* block_tuples = scratch;
