@@ -11,6 +11,7 @@ Workloads (BASELINE.json configs):
   dense_1m    2^20 rows/GPU x 1004 features, 20 iterations  (configs[1]; the default)
   dense_16m   2^24 rows/GPU x 1004 features, 50 iterations  (configs[2], HBM-roofline config; no e2e:
               134.75 GB does not stage through host memory)
+  dense_d128  2^24 rows/GPU x 128 features, 50 iterations (the narrow-row shape of configs[3])
   csr_2m      2^21 rows/GPU, 2^20+4 columns, ~24 nnz/row CSR, 50 iterations (configs[4] per GPU)
 Multi-GPU: every rank holds the same number of rows (weak scaling); per iteration the ranks exchange
 their (gradSum, lossSum, count) shard vectors with one NCCL all-gather.
@@ -29,6 +30,8 @@ sys.path.insert(0, ROOT)
 WORKLOADS = {
     "dense_1m": dict(rows=1 << 20, d=1004, iters=20, step=0.1),
     "dense_16m": dict(rows=1 << 24, d=1004, iters=50, step=0.1),
+    # configs[3] strong-scaling shape (2^27 x 128 over the GPUs): here 2^24 narrow rows per GPU
+    "dense_d128": dict(rows=1 << 24, d=128, iters=50, step=0.1),
     # configs[4] per GPU: 2^21 rows (2^24 over 8 GPUs), 2^20 hashed + 4 numeric columns, ~24 nnz/row, uniform columns
     "csr_2m": dict(rows=1 << 21, d=(1 << 20) + 4, d_text=1 << 20, iters=50, step=0.005, csr=True),
 }
@@ -283,7 +286,7 @@ def main():
                 "wall_ms_per_step": wall_ms / args.steps,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": traffic, "peak_source": peak_src,
-                             "kernel": "k_csr_rows + k_csr_cols + k_csr_fold (one read of the CSR credited)" if csr else "k_dense_iter<1,TRAIN,RL1>",
+                             "kernel": "k_csr_rows + k_csc_windows + k_csc_edges (one read of the CSR credited)" if csr else ("k_dense_iter<1,TRAIN,RL1>" if d + 1 > 992 else "k_dense_iter<1,TRAIN,row lanes>"),
                              "kernel_ms": kern_ms_per_launch, "bytes_per_launch": int(kbytes),
                              "frac_of_nominal_8TBs": achieved / 8000.0},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": launches}
