@@ -198,13 +198,24 @@ static __global__ void __launch_bounds__(256) k_csc_windows(const CscView c, con
         double carry = 0.0;      // running sum of the segment left open by the previous round
         bool carry_head = false; // ... and whether that segment's head lies in this window
         unsigned hnext = 0;
+        // all of the window's loads first (8 streaming pairs, then 8 gathers of diff in flight per lane)
+        double prod[8];
+        int ri[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const long long e = base + i * 32 + lane;
+            const bool in = e < c.nnz;
+            ri[i] = in ? c.rowidx[e] : -1;
+            prod[i] = in ? c.cvals[e] : 0.0;
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) prod[i] = ri[i] >= 0 ? diff[ri[i]] * prod[i] : 0.0;
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             const unsigned hm = __shfl_sync(0xffffffffu, myword, i);
             hnext = __shfl_sync(0xffffffffu, myword, i + 1);
             const long long e = base + i * 32 + lane;
-            double v = 0.0;
-            if (e < c.nnz) v = diff[c.rowidx[e]] * c.cvals[e];
+            double v = prod[i];
             const unsigned hb = hm & le;
             const int seg_start = hb ? 31 - __clz(hb) : -1;
 #pragma unroll
