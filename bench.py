@@ -12,6 +12,8 @@ Workloads (BASELINE.json configs):
   dense_16m   2^24 rows/GPU x 1004 features, 50 iterations  (configs[2], HBM-roofline config; no e2e:
               134.75 GB does not stage through host memory)
   dense_d128  2^24 rows/GPU x 128 features, 50 iterations (the narrow-row shape of configs[3])
+  tweets_1m   10^6 synthetic tweets/GPU (SURVEY 8d config 1 recipe) -> device featuriser (HashingTF(1000) + 4) ->
+              CSR of the rows that pass the retweet filter (~14 %), 50 iterations, reference step size 0.005
   csr_2m      2^21 rows/GPU, 2^20+4 columns, ~24 nnz/row CSR, 50 iterations (configs[4] per GPU)
 Multi-GPU: every rank holds the same number of rows (weak scaling); per iteration the ranks exchange
 their (gradSum, lossSum, count) shard vectors with one NCCL all-gather.
@@ -35,6 +37,7 @@ WORKLOADS = {
     # configs[4] per GPU: 2^21 rows (2^24 over 8 GPUs), 2^20 hashed + 4 numeric columns, ~24 nnz/row, uniform columns
     "csr_2m": dict(rows=1 << 21, d=(1 << 20) + 4, d_text=1 << 20, iters=50, step=0.005, csr=True),
 }
+WORKLOADS["tweets_1m"] = dict(rows=1000000, d=1004, iters=50, step=0.005, csr=True, tweets=True)
 METRIC = "sgd_row_iterations_per_s"
 UNIT = "row*iter/s"
 
@@ -45,6 +48,35 @@ def measured_peak():
             return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
     except Exception:
         return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def synth_tweets(n, seed):
+    """Vectorised form of the SURVEY.md 8d config-1 recipe: lower-case text of U[2,140] tokens over letters, digits,
+    punctuation, 16 Latin-1 accented letters and 8 emoji (two UTF-16 units each); retweet ~ Bernoulli(0.7); log-uniform
+    counts; created within 7 days before a fixed now.  -> (TweetBatch columns, now_ms)"""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    now = 1464739200000
+    one = [ord(c) for c in "abcdefghijklmnopqrstuvwxyz0123456789 #@.,!?:/" + "\u00e0\u00e1\u00e2\u00e3\u00e4\u00e5\u00e7\u00e8\u00e9\u00ea\u00eb\u00ec\u00ed\u00f1\u00f6\u00fc"]
+    emoji = [0x1F600, 0x1F601, 0x1F602, 0x1F923, 0x1F60D, 0x1F44D, 0x1F525, 0x1F389]
+    first = np.array(one + [0xD800 + ((c - 0x10000) >> 10) for c in emoji], np.uint16)
+    second = np.array([0] * len(one) + [0xDC00 + ((c - 0x10000) & 0x3FF) for c in emoji], np.uint16)
+    tlen = np.array([1] * len(one) + [2] * len(emoji), np.int64)
+    ntok = rng.integers(2, 141, n)
+    tok = rng.integers(0, len(first), int(ntok.sum()))
+    ulen = tlen[tok]
+    pos = np.cumsum(ulen) - ulen
+    units = np.zeros(int(ulen.sum()), np.uint16)
+    units[pos] = first[tok]
+    two = ulen == 2
+    units[pos[two] + 1] = second[tok[two]]
+    tok_end = np.cumsum(ntok)
+    cum_units = np.concatenate([[0], np.cumsum(ulen)])
+    text_off = np.concatenate([[0], cum_units[tok_end]]).astype(np.int64)
+    lu = lambda lo, hi: np.floor(np.exp(rng.uniform(np.log(lo), np.log(hi), n))).astype(np.int64)
+    cols = dict(text_utf16=units, text_off=text_off, retweet_count=lu(1, 1e5), followers=lu(1, 1e8), favourites=lu(1, 1e5) - 1,
+                friends=lu(1, 1e5) - 1, created_ms=now - rng.integers(0, 7 * 86400_000, n), is_retweet=(rng.random(n) < 0.7))
+    return cols, now
 
 
 class ClockSampler:
@@ -134,6 +166,7 @@ def main():
     ap.add_argument("--rows", type=int, default=0, help="override rows per GPU (testing)")
     ap.add_argument("--iters", type=int, default=0, help="override SGD iterations per micro-batch (testing)")
     ap.add_argument("--e2e-steps", type=int, default=4)
+    ap.add_argument("--e2e-sync", action="store_true", help="blocking ingest in the e2e leg (A/B against the pipelined default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     wl = dict(WORKLOADS[args.workload])
@@ -184,7 +217,13 @@ def main():
     model = (tw.StreamingLinearRegressionWithSGD(ctx=ctx).setNumIterations(iters).setStepSize(wl["step"])
              .setMiniBatchFraction(1.0).setConvergenceTol(0.0).setInitialWeights(tw.Vectors.zeros(d)))
     csr = bool(wl.get("csr"))
-    if csr:
+    tweets = None
+    if wl.get("tweets"):
+        cols, now_ms = synth_tweets(n, 20160601 + rank)
+        tweets = tw.TweetBatch.from_arrays(**cols)
+        batch = ctx.batch_from_tweets(tweets, now_ms)                # filter + featurise on the GPU
+        n_tweets, n = n, batch.n                                     # the metric counts the rows that train
+    elif csr:
         batch = ctx.batch_synth_csr(n, wl["d_text"], seed=42, row0=rank * n)
     else:
         batch = ctx.batch_synth_dense(n, d, seed=42, row0=rank * n)  # resident in HBM before the timed region
@@ -218,7 +257,11 @@ def main():
     # ---- end to end through the C ABI with HOST buffers: ingest (H2D) + stats + train + results (D2H)
     e2e = None
     if (args.workload != "dense_16m" or args.rows) and args.e2e_steps > 0:
-        if csr:
+        if tweets is not None:
+            h2d = sum(getattr(tweets, k).nbytes for k in ("text_utf16", "text_off", "retweet_count", "followers", "favourites",
+                                                           "friends", "created_ms", "is_retweet"))
+            make = lambda: ctx.batch_from_tweets(tweets, now_ms)
+        elif csr:
             host = batch.export_csr()                                  # host copy of this rank's rows
             h2d = sum(a.nbytes for a in host)
             make = lambda: ctx.batch_from_csr(n, d, *host)
@@ -230,7 +273,7 @@ def main():
             h2d = n * (d + 1) * 8
             # page-locked buffers: the library DMAs straight from them on its copy stream, so the ingest of
             # step t+1 is issued before step t computes and overlaps it (streaming ingest)
-            make = lambda: ctx.batch_from_dense_async(Xp, yp)
+            make = (lambda: ctx.batch_from_dense(Xp, yp)) if args.e2e_sync else (lambda: ctx.batch_from_dense_async(Xp, yp))
         model.setInitialWeights(tw.Vectors.zeros(d))
         t_ingest = t_step = 0.0
 
@@ -280,7 +323,7 @@ def main():
                 "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f64", "data": "synthetic",
                 "config": {"workload": args.workload, "rows_per_gpu": n, "features": d, "sgd_iterations": iters,
-                           "convergence_tol": 0.0, "parallelism": "rows sharded x%d, NCCL all-gather of shard partials per iteration" % world,
+                           "convergence_tol": 0.0, **({"tweets_per_gpu": n_tweets, "nnz_per_gpu": batch.nnz} if tweets is not None else {}), "parallelism": "rows sharded x%d, NCCL all-gather of shard partials per iteration" % world,
                            "l2": "inputs (%.2f GB/GPU) larger than L2; no flush needed" % ((batch.nnz * 12 * 2 + n * 24) / 1e9 if csr else n * (d + 2) * 8 / 1e9),
                            "timing": "CUDA events on the library stream around each step's iteration loop, max over ranks"},
                 "wall_ms_per_step": wall_ms / args.steps,

@@ -478,6 +478,20 @@ class TweetBatch:
         self.created_ms = np.ascontiguousarray(created_ms, np.int64)
         self.is_retweet = np.ascontiguousarray(is_retweet, np.uint8)
 
+    @classmethod
+    def from_arrays(cls, text_utf16, text_off, retweet_count, followers, favourites, friends, created_ms, is_retweet):
+        """Already packed columns (text as one uint16 array + n+1 offsets)."""
+        self = cls.__new__(cls)
+        self.text_utf16 = np.ascontiguousarray(text_utf16, np.uint16)
+        self.text_off = np.ascontiguousarray(text_off, np.int64)
+        self.retweet_count = np.ascontiguousarray(retweet_count, np.int32)
+        self.followers = np.ascontiguousarray(followers, np.int32)
+        self.favourites = np.ascontiguousarray(favourites, np.int32)
+        self.friends = np.ascontiguousarray(friends, np.int32)
+        self.created_ms = np.ascontiguousarray(created_ms, np.int64)
+        self.is_retweet = np.ascontiguousarray(is_retweet, np.uint8)
+        return self
+
     def __len__(self):
         return int(self.retweet_count.shape[0])
 
