@@ -46,6 +46,7 @@ struct twtml_ctx {
     int nshards = twtml::kMaxShards;
     cudaStream_t stream = nullptr;
     cudaStream_t copy_stream = nullptr; // asynchronous ingest (twtml_batch_from_dense_async)
+    cudaMemPool_t pool = nullptr;       // batch memory: stream-ordered, kept across batches (no OS round trip, no device-wide sync)
     ncclComm_t comm = nullptr;
     std::mutex mu;
     int live_handles = 0; // models + batches created on this context and not yet freed
@@ -105,6 +106,9 @@ int upload_plain(twtml_ctx* ctx, void* dst, const void* src, size_t bytes);
 int ctx_global_rows(twtml_ctx* ctx, int64_t n_local, int64_t* n_global, int64_t* row0);
 void make_plan(int64_t n_local, int spr, int R, Plan& p);
 void batch_free_locked(twtml_batch* b);
+// batch memory from the context's pool, ordered on the compute stream
+int pool_alloc(twtml_ctx* ctx, void** p, size_t bytes);
+void pool_free(twtml_ctx* ctx, void* p);
 // launch shape of the dense iteration kernel for a feature width
 struct DenseCfg {
     int cp, c2, c2p, rl, R, nstages, grid_per_sm;

@@ -192,6 +192,30 @@ int ctx_global_rows(twtml_ctx* ctx, int64_t n_local, int64_t* n_global, int64_t*
     return 0;
 }
 
+int pool_alloc(twtml_ctx* ctx, void** p, size_t bytes)
+{
+    *p = nullptr;
+    if (bytes == 0) bytes = 8;
+    cudaError_t e = cudaMallocFromPoolAsync(p, bytes, ctx->pool, ctx->stream);
+    if (e != cudaSuccess) { // give cached blocks back and try once more
+        cudaGetLastError();
+        cudaStreamSynchronize(ctx->stream);
+        cudaMemPoolTrimTo(ctx->pool, 0);
+        e = cudaMallocFromPoolAsync(p, bytes, ctx->pool, ctx->stream);
+    }
+    if (e != cudaSuccess) {
+        *p = nullptr;
+        cudaGetLastError();
+        return fail(TWTML_E_OOM, "device allocation of %zu bytes: %s", bytes, cudaGetErrorString(e));
+    }
+    return 0;
+}
+
+void pool_free(twtml_ctx* ctx, void* p)
+{
+    if (p) cudaFreeAsync(p, ctx->stream);
+}
+
 static int ensure_pinned(twtml_ctx* ctx, size_t bytes)
 {
     if (ctx->pin_bytes >= bytes) return 0;
@@ -226,10 +250,30 @@ int staged_upload(twtml_ctx* ctx, void* dst, size_t unit_bytes, int64_t n_units,
     }
     return 0;
 }
+static void parallel_rows(int64_t n, int64_t min_per_thread, const std::function<void(int64_t, int64_t)>& fn);
+static bool page_locked(const void* p);
+
+// Host -> device copy of a plain array: straight DMA when the caller's memory is page-locked, else through
+// the pinned ring with the staging memcpy spread over host threads.
 int upload_plain(twtml_ctx* ctx, void* dst, const void* src, size_t bytes)
 {
+    if (bytes == 0) return 0;
+    if (page_locked(src)) {
+        TW_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+        return 0;
+    }
     const char* s = static_cast<const char*>(src);
-    return staged_upload(ctx, dst, 1, (int64_t)bytes, [s](char* out, int64_t u0, int64_t nu) { memcpy(out, s + u0, (size_t)nu); });
+    return staged_upload(ctx, dst, 1, (int64_t)bytes, [s](char* out, int64_t u0, int64_t nu) {
+        parallel_rows(nu, 4 << 20, [&](int64_t lo, int64_t hi) { memcpy(out + lo, s + u0 + lo, (size_t)(hi - lo)); });
+    });
+}
+
+static bool page_locked(const void* p)
+{
+    cudaPointerAttributes pa{};
+    const bool yes = cudaPointerGetAttributes(&pa, p) == cudaSuccess && pa.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+    return yes;
 }
 
 static void parallel_rows(int64_t n, int64_t min_per_thread, const std::function<void(int64_t, int64_t)>& fn)
@@ -521,7 +565,7 @@ void batch_free_locked(twtml_batch* b)
     for (void* p : {(void*)b->X, (void*)b->rowptr, (void*)b->colidx, (void*)b->vals, (void*)b->labels, (void*)b->colptr, (void*)b->rowidx,
                     (void*)b->cvals, (void*)b->headbits, (void*)b->nzcol, (void*)b->win_first_nz, (void*)b->wkey, (void*)b->win_first_part,
                     (void*)b->win_last_part, (void*)b->diff})
-        cudaFree(p);
+        pool_free(b->ctx, p);
     b->ctx->live_handles -= 1;
     delete b;
 }
@@ -570,6 +614,16 @@ static int32_t create_common(int32_t device, int32_t rank, int32_t world, const 
     cudaError_t se = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
     if (se != cudaSuccess) { delete c; return fail(TWTML_E_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(se)); }
     cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
+    {
+        cudaMemPoolProps props{};
+        props.allocType = cudaMemAllocationTypePinned;
+        props.location.type = cudaMemLocationTypeDevice;
+        props.location.id = device;
+        cudaError_t pe = cudaMemPoolCreate(&c->pool, &props);
+        if (pe != cudaSuccess) { cudaStreamDestroy(c->stream); delete c; return fail(TWTML_E_CUDA, "cudaMemPoolCreate: %s", cudaGetErrorString(pe)); }
+        unsigned long long keep = ~0ull; // freed batch memory stays cached for the next micro-batch
+        cudaMemPoolSetAttribute(c->pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    }
     for (int i = 0; i < 2; ++i) cudaEventCreateWithFlags(&c->pin_ev[i], cudaEventDisableTiming);
     if (world > 1) {
         if (!nccl_api().ok) { delete c; return fail(TWTML_E_NCCL, "libnccl.so.2 could not be loaded: %s", dlerror()); }
@@ -621,6 +675,7 @@ int32_t twtml_destroy(twtml_ctx* ctx)
         if (ctx->pin_ev[i]) cudaEventDestroy(ctx->pin_ev[i]);
     }
     for (cudaEvent_t e : ctx->ev) cudaEventDestroy(e);
+    if (ctx->pool) cudaMemPoolDestroy(ctx->pool);
     cudaStreamDestroy(ctx->stream);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     delete ctx;
@@ -759,11 +814,11 @@ static int32_t new_dense(twtml_ctx* ctx, int64_t n, int64_t d, twtml_batch** out
     b->ldx = (d + 2) & ~(int64_t)1;
     make_plan(n, ctx->spr, c.R, b->plan);
     if (n > 0) {
-        cudaError_t e = cudaMalloc(&b->X, sizeof(double) * (size_t)n * (size_t)b->ldx);
-        if (e != cudaSuccess) { delete b; return fail(TWTML_E_OOM, "cudaMalloc(%lld x %lld doubles): %s", (long long)n, (long long)b->ldx, cudaGetErrorString(e)); }
+        int rc0 = pool_alloc(ctx, reinterpret_cast<void**>(&b->X), sizeof(double) * (size_t)n * (size_t)b->ldx);
+        if (rc0) { delete b; return rc0; }
     }
     int rc = ctx_global_rows(ctx, n, &b->n_global, &b->row0_global);
-    if (rc) { cudaFree(b->X); delete b; return rc; }
+    if (rc) { pool_free(ctx, b->X); delete b; return rc; }
     ctx->live_handles += 1;
     *out = b;
     return 0;
@@ -804,18 +859,10 @@ int32_t twtml_batch_from_dense(twtml_ctx* ctx, int64_t n, int64_t d, const doubl
             });
         }
         if (!rc && cudaStreamSynchronize(ctx->stream) != cudaSuccess) rc = fail(TWTML_E_CUDA, "upload failed: %s", cudaGetErrorString(cudaGetLastError()));
-        if (rc) { cudaFree(b->X); ctx->live_handles -= 1; delete b; return rc; }
+        if (rc) { pool_free(ctx, b->X); ctx->live_handles -= 1; delete b; return rc; }
     }
     *out = b;
     return 0;
-}
-
-static bool page_locked(const void* p)
-{
-    cudaPointerAttributes pa{};
-    const bool yes = cudaPointerGetAttributes(&pa, p) == cudaSuccess && pa.type == cudaMemoryTypeHost;
-    cudaGetLastError();
-    return yes;
 }
 
 int32_t twtml_batch_from_dense_async(twtml_ctx* ctx, int64_t n, int64_t d, const double* X, int64_t ld_x, const double* labels, twtml_batch** out)
@@ -828,8 +875,11 @@ int32_t twtml_batch_from_dense_async(twtml_ctx* ctx, int64_t n, int64_t d, const
     Guard g(ctx);
     twtml_batch* b = nullptr;
     TW_TRY(new_dense(ctx, n, d, &b));
-    cudaError_t e = cudaMalloc(&b->labels, sizeof(double) * (size_t)n);
-    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&b->ready, cudaEventDisableTiming);
+    if (int rc = pool_alloc(ctx, reinterpret_cast<void**>(&b->labels), sizeof(double) * (size_t)n)) { batch_free_locked(b); return rc; }
+    cudaError_t e = cudaEventCreateWithFlags(&b->ready, cudaEventDisableTiming);
+    // the two buffers were allocated in compute-stream order: the copy stream may touch them only after that point
+    if (e == cudaSuccess) e = cudaEventRecord(b->ready, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(ctx->copy_stream, b->ready, 0);
     if (e == cudaSuccess) e = cudaMemcpy2DAsync(b->X, (size_t)b->ldx * 8, X, (size_t)ld_x * 8, (size_t)d * 8, (size_t)n, cudaMemcpyHostToDevice, ctx->copy_stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(b->labels, labels, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, ctx->copy_stream);
     if (e == cudaSuccess) {
@@ -877,7 +927,7 @@ int32_t twtml_batch_synth_dense(twtml_ctx* ctx, int64_t n, int64_t d, uint64_t s
         k_synth_dense_y<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(b->X, b->ldx, (int)d, seed, row0, inv, n);
         cudaError_t e = cudaGetLastError();
         if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-        if (e != cudaSuccess) { cudaFree(b->X); ctx->live_handles -= 1; delete b; return fail(TWTML_E_CUDA, "synthetic generator: %s", cudaGetErrorString(e)); }
+        if (e != cudaSuccess) { pool_free(ctx, b->X); ctx->live_handles -= 1; delete b; return fail(TWTML_E_CUDA, "synthetic generator: %s", cudaGetErrorString(e)); }
     }
     *out = b;
     return 0;

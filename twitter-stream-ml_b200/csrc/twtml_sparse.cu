@@ -6,8 +6,10 @@
 #include <cub/device/device_scan.cuh>
 
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstring>
+#include <thread>
 #include <vector>
 
 #include "csr.cuh"
@@ -20,12 +22,9 @@
 namespace twtml {
 
 template <class T>
-static int dev_alloc(T** p, size_t count)
+static int dev_alloc(twtml_ctx* ctx, T** p, size_t count)
 {
-    *p = nullptr;
-    cudaError_t e = cudaMalloc(reinterpret_cast<void**>(p), sizeof(T) * std::max<size_t>(count, 1));
-    if (e != cudaSuccess) return fail(TWTML_E_OOM, "cudaMalloc(%zu bytes): %s", sizeof(T) * count, cudaGetErrorString(e));
-    return 0;
+    return pool_alloc(ctx, reinterpret_cast<void**>(p), sizeof(T) * std::max<size_t>(count, 1));
 }
 
 static int exclusive_sum(twtml_ctx* ctx, const long long* in, long long* out, long long n)
@@ -51,22 +50,22 @@ static int csr_finalize(twtml_ctx* ctx, twtml_batch* b)
     const long long nnz = b->nnz;
     const long long nwin = (nnz + kWin - 1) / kWin;
     b->nwin = nwin;
-    TW_TRY(dev_alloc(&b->colptr, (size_t)d + 1));
-    TW_TRY(dev_alloc(&b->rowidx, (size_t)nnz));
-    TW_TRY(dev_alloc(&b->cvals, (size_t)nnz));
-    TW_TRY(dev_alloc(&b->diff, (size_t)b->n));
-    TW_TRY(dev_alloc(&b->headbits, (size_t)(nwin + 1) * 8));
-    TW_TRY(dev_alloc(&b->win_first_nz, (size_t)nwin + 1));
-    TW_TRY(dev_alloc(&b->wkey, (size_t)nwin + 1));
-    TW_TRY(dev_alloc(&b->win_first_part, (size_t)nwin + 1));
-    TW_TRY(dev_alloc(&b->win_last_part, (size_t)nwin + 1));
-    TW_TRY(dev_alloc(&b->nzcol, (size_t)std::min<long long>(nnz, d) + 1));
+    TW_TRY(dev_alloc(ctx, &b->colptr, (size_t)d + 1));
+    TW_TRY(dev_alloc(ctx, &b->rowidx, (size_t)nnz));
+    TW_TRY(dev_alloc(ctx, &b->cvals, (size_t)nnz));
+    TW_TRY(dev_alloc(ctx, &b->diff, (size_t)b->n));
+    TW_TRY(dev_alloc(ctx, &b->headbits, (size_t)(nwin + 1) * 8));
+    TW_TRY(dev_alloc(ctx, &b->win_first_nz, (size_t)nwin + 1));
+    TW_TRY(dev_alloc(ctx, &b->wkey, (size_t)nwin + 1));
+    TW_TRY(dev_alloc(ctx, &b->win_first_part, (size_t)nwin + 1));
+    TW_TRY(dev_alloc(ctx, &b->win_last_part, (size_t)nwin + 1));
+    TW_TRY(dev_alloc(ctx, &b->nzcol, (size_t)std::min<long long>(nnz, d) + 1));
     TW_CUDA(cudaMemsetAsync(b->headbits, 0, sizeof(unsigned) * (size_t)(nwin + 1) * 8, ctx->stream));
     if (nnz > 0) {
         int *keys_out = nullptr, *iota = nullptr, *perm = nullptr;
-        TW_TRY(dev_alloc(&keys_out, (size_t)nnz));
-        TW_TRY(dev_alloc(&iota, (size_t)nnz));
-        TW_TRY(dev_alloc(&perm, (size_t)nnz));
+        TW_TRY(dev_alloc(ctx, &keys_out, (size_t)nnz));
+        TW_TRY(dev_alloc(ctx, &iota, (size_t)nnz));
+        TW_TRY(dev_alloc(ctx, &perm, (size_t)nnz));
         int rc = 0;
         do {
             k_iota<<<blocks_for(nnz, 256), 256, 0, ctx->stream>>>(iota, nnz);
@@ -87,7 +86,7 @@ static int csr_finalize(twtml_ctx* ctx, twtml_batch* b)
             long long* winheads = reinterpret_cast<long long*>(iota); // iota is dead from here on; nnz ints >= nwin+1 int64 when nnz >= 2
             long long* winheads_own = nullptr;
             if ((size_t)nnz * sizeof(int) < (size_t)(nwin + 1) * sizeof(long long)) {
-                if ((rc = dev_alloc(&winheads_own, (size_t)nwin + 1))) break;
+                if ((rc = dev_alloc(ctx, &winheads_own, (size_t)nwin + 1))) break;
                 winheads = winheads_own;
             }
             k_csc_winmeta<<<blocks_for(nwin + 1, 256), 256, 0, ctx->stream>>>(b->headbits, keys_out, nnz, nwin, winheads, b->wkey);
@@ -95,12 +94,12 @@ static int csr_finalize(twtml_ctx* ctx, twtml_batch* b)
             if (!rc) k_csc_nzcol<<<blocks_for(nnz, 256), 256, 0, ctx->stream>>>(keys_out, b->headbits, b->win_first_nz, nnz, b->nzcol);
             if (!rc && cudaGetLastError() != cudaSuccess) rc = fail(TWTML_E_CUDA, "transpose kernels failed to launch");
             cudaStreamSynchronize(ctx->stream);
-            cudaFree(winheads_own);
+            pool_free(ctx, winheads_own);
         } while (0);
         cudaStreamSynchronize(ctx->stream);
-        cudaFree(keys_out);
-        cudaFree(iota);
-        cudaFree(perm);
+        pool_free(ctx, keys_out);
+        pool_free(ctx, iota);
+        pool_free(ctx, perm);
         if (rc) return rc;
     } else {
         TW_CUDA(cudaMemsetAsync(b->colptr, 0, sizeof(long long) * ((size_t)d + 1), ctx->stream));
@@ -118,10 +117,10 @@ static int new_csr(twtml_ctx* ctx, int64_t n, int64_t d, int64_t nnz, twtml_batc
     b->d = d;
     b->nnz = nnz;
     ctx->live_handles += 1; // released by twtml_batch_free, also on the failure paths below and in the callers
-    int rc = dev_alloc(&b->rowptr, (size_t)n + 1);
-    if (!rc) rc = dev_alloc(&b->colidx, (size_t)nnz);
-    if (!rc) rc = dev_alloc(&b->vals, (size_t)nnz);
-    if (!rc) rc = dev_alloc(&b->labels, (size_t)n);
+    int rc = dev_alloc(ctx, &b->rowptr, (size_t)n + 1);
+    if (!rc) rc = dev_alloc(ctx, &b->colidx, (size_t)nnz);
+    if (!rc) rc = dev_alloc(ctx, &b->vals, (size_t)nnz);
+    if (!rc) rc = dev_alloc(ctx, &b->labels, (size_t)n);
     if (rc) { batch_free_locked(b); return rc; }
     *out = b;
     return 0;
@@ -208,11 +207,26 @@ int32_t twtml_batch_from_csr(twtml_ctx* ctx, int64_t n, int64_t d, const int64_t
     if (n < 0 || d < 1 || d > ((int64_t)1 << 30) || !rowptr || (n > 0 && !labels)) return fail(TWTML_E_INVALID_ARG, "twtml_batch_from_csr: bad shape or null data");
     const int64_t nnz = rowptr[n] - rowptr[0];
     if (rowptr[0] != 0 || nnz < 0 || (nnz > 0 && (!colidx || !vals))) return fail(TWTML_E_INVALID_ARG, "twtml_batch_from_csr: rowptr must start at 0 and be non-decreasing");
-    for (int64_t r = 0; r < n; ++r) { // Vectors.sparse require()s strictly increasing, in-range indices [U]
-        if (rowptr[r + 1] < rowptr[r]) return fail(TWTML_E_INVALID_ARG, "rowptr decreases at row %lld", (long long)r);
-        for (int64_t k = rowptr[r]; k < rowptr[r + 1]; ++k)
-            if (colidx[k] < 0 || colidx[k] >= d || (k > rowptr[r] && colidx[k] <= colidx[k - 1]))
-                return fail(TWTML_E_INVALID_ARG, "row %lld: indices must be strictly increasing and < %lld", (long long)r, (long long)d);
+    { // Vectors.sparse require()s strictly increasing, in-range indices [U]; checked on all host threads
+        std::atomic<int64_t> bad_row(-1);
+        const unsigned hw = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+        const int nt = (int)std::min<int64_t>(hw, std::max<int64_t>(1, n / 4096));
+        auto scan = [&](int64_t lo, int64_t hi) {
+            for (int64_t r = lo; r < hi && bad_row.load(std::memory_order_relaxed) < 0; ++r) {
+                bool ok = rowptr[r + 1] >= rowptr[r];
+                for (int64_t k = rowptr[r]; ok && k < rowptr[r + 1]; ++k)
+                    ok = colidx[k] >= 0 && colidx[k] < d && (k == rowptr[r] || colidx[k] > colidx[k - 1]);
+                if (!ok) bad_row.store(r);
+            }
+        };
+        if (nt <= 1) scan(0, n);
+        else {
+            std::vector<std::thread> th;
+            for (int i = 0; i < nt; ++i) th.emplace_back(scan, n * i / nt, n * (i + 1) / nt);
+            for (auto& t : th) t.join();
+        }
+        if (bad_row.load() >= 0)
+            return fail(TWTML_E_INVALID_ARG, "row %lld: rowptr must not decrease and indices must be strictly increasing and < %lld", (long long)bad_row.load(), (long long)d);
     }
     Guard g(ctx);
     twtml_batch* b = nullptr;
@@ -233,15 +247,15 @@ int32_t twtml_batch_synth_csr(twtml_ctx* ctx, int64_t n, int32_t d_text, uint64_
     if (n < 0 || d_text < 1) return fail(TWTML_E_INVALID_ARG, "twtml_batch_synth_csr: bad shape");
     Guard g(ctx);
     long long *rownnz = nullptr, *rowptr = nullptr;
-    TW_TRY(dev_alloc(&rownnz, (size_t)n + 1));
-    TW_TRY(dev_alloc(&rowptr, (size_t)n + 1));
+    TW_TRY(dev_alloc(ctx, &rownnz, (size_t)n + 1));
+    TW_TRY(dev_alloc(ctx, &rowptr, (size_t)n + 1));
     TW_CUDA(cudaMemsetAsync(rownnz, 0, sizeof(long long) * ((size_t)n + 1), ctx->stream));
     if (n > 0) k_synth_csr_count<<<blocks_for(n, 128), 128, 0, ctx->stream>>>(rownnz, n, d_text, seed, row0);
     int rc = exclusive_sum(ctx, rownnz, rowptr, n + 1);
     long long nnz = 0;
     if (!rc && cudaMemcpyAsync(&nnz, rowptr + n, sizeof(nnz), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) rc = fail(TWTML_E_CUDA, "nnz copy failed");
     cudaStreamSynchronize(ctx->stream);
-    cudaFree(rownnz);
+    pool_free(ctx, rownnz);
     twtml_batch* b = nullptr;
     if (!rc) rc = new_csr(ctx, n, (int64_t)d_text + 4, nnz, &b);
     if (!rc) {
@@ -250,7 +264,7 @@ int32_t twtml_batch_synth_csr(twtml_ctx* ctx, int64_t n, int32_t d_text, uint64_
         if (cudaGetLastError() != cudaSuccess) rc = fail(TWTML_E_CUDA, "synthetic CSR generator failed to launch");
     }
     cudaStreamSynchronize(ctx->stream);
-    cudaFree(rowptr);
+    pool_free(ctx, rowptr);
     if (!rc) rc = csr_finalize(ctx, b);
     if (rc) { batch_free_locked(b); return rc; }
     *out = b;
@@ -285,24 +299,24 @@ int32_t twtml_batch_from_tweets(twtml_ctx* ctx, const uint16_t* text_utf16, cons
     int *d_rc = nullptr, *d_fo = nullptr, *d_fa = nullptr, *d_fr = nullptr, *pair_idx = nullptr, *pair_cnt = nullptr, *d_maxlen = nullptr;
     uint8_t* d_rt = nullptr;
     std::vector<void*> owned;
-    auto cleanup = [&]() { for (void* p : owned) cudaFree(p); };
+    auto cleanup = [&]() { for (void* p : owned) pool_free(ctx, p); };
 #define TW_OWN(call, ptrvar) do { int rc_ = (call); if (rc_) { cleanup(); return rc_; } owned.push_back(ptrvar); } while (0)
 #define TW_DO(call) do { int rc_ = (call); if (rc_) { cleanup(); return rc_; } } while (0)
-    TW_OWN(dev_alloc(&d_text, (size_t)units), d_text);
-    TW_OWN(dev_alloc(&d_off, (size_t)n + 1), d_off);
-    TW_OWN(dev_alloc(&d_created, (size_t)n), d_created);
-    TW_OWN(dev_alloc(&d_rc, (size_t)n), d_rc);
-    TW_OWN(dev_alloc(&d_fo, (size_t)n), d_fo);
-    TW_OWN(dev_alloc(&d_fa, (size_t)n), d_fa);
-    TW_OWN(dev_alloc(&d_fr, (size_t)n), d_fr);
-    TW_OWN(dev_alloc(&d_rt, (size_t)n), d_rt);
-    TW_OWN(dev_alloc(&pair_idx, (size_t)units), pair_idx);
-    TW_OWN(dev_alloc(&pair_cnt, (size_t)units), pair_cnt);
-    TW_OWN(dev_alloc(&keep, (size_t)n + 1), keep);
-    TW_OWN(dev_alloc(&rownnz, (size_t)n + 1), rownnz);
-    TW_OWN(dev_alloc(&krow, (size_t)n + 1), krow);
-    TW_OWN(dev_alloc(&eoff, (size_t)n + 1), eoff);
-    TW_OWN(dev_alloc(&d_maxlen, 1), d_maxlen);
+    TW_OWN(dev_alloc(ctx, &d_text, (size_t)units), d_text);
+    TW_OWN(dev_alloc(ctx, &d_off, (size_t)n + 1), d_off);
+    TW_OWN(dev_alloc(ctx, &d_created, (size_t)n), d_created);
+    TW_OWN(dev_alloc(ctx, &d_rc, (size_t)n), d_rc);
+    TW_OWN(dev_alloc(ctx, &d_fo, (size_t)n), d_fo);
+    TW_OWN(dev_alloc(ctx, &d_fa, (size_t)n), d_fa);
+    TW_OWN(dev_alloc(ctx, &d_fr, (size_t)n), d_fr);
+    TW_OWN(dev_alloc(ctx, &d_rt, (size_t)n), d_rt);
+    TW_OWN(dev_alloc(ctx, &pair_idx, (size_t)units), pair_idx);
+    TW_OWN(dev_alloc(ctx, &pair_cnt, (size_t)units), pair_cnt);
+    TW_OWN(dev_alloc(ctx, &keep, (size_t)n + 1), keep);
+    TW_OWN(dev_alloc(ctx, &rownnz, (size_t)n + 1), rownnz);
+    TW_OWN(dev_alloc(ctx, &krow, (size_t)n + 1), krow);
+    TW_OWN(dev_alloc(ctx, &eoff, (size_t)n + 1), eoff);
+    TW_OWN(dev_alloc(ctx, &d_maxlen, 1), d_maxlen);
     if (units) TW_DO(upload_plain(ctx, d_text, text_utf16, sizeof(uint16_t) * (size_t)units));
     TW_DO(upload_plain(ctx, d_off, text_off, sizeof(int64_t) * (size_t)(n + 1)));
     TW_DO(upload_plain(ctx, d_created, created_ms, sizeof(int64_t) * (size_t)n));
