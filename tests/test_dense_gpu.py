@@ -68,7 +68,7 @@ def test_stats_golden(tw, ctx):
 # (n, d): tiny / ragged row counts, the three column-pass shapes (d=4,128,1004 -> CP=1; 1500 -> CP=2;
 # 3000 -> CP=4), row lanes > 1 (d=4, 128), odd d (label shares a column pair with the last feature)
 SHAPES = [(1, 4), (7, 4), (1000, 4), (513, 127), (4099, 128), (2500, 1004), (20000, 1004), (777, 1500), (300, 3000),
-          (100, 1, ), (3, 2), (90, 1022), (100, 1023), (64, 1024), (50, 2047), (40, 2048), (30, 4095)]   # the width limits of each kernel form
+          (100, 1, ), (3, 2), (90, 1022), (100, 1023), (64, 1024), (60, 1025), (50, 2047), (40, 2048), (35, 2049), (30, 4095), (20, 4096)]   # the width limits of each kernel form
 
 
 @pytest.mark.parametrize("n,d", SHAPES)
@@ -89,7 +89,7 @@ def test_train_matches_oracle(tw, ctx, oracle, n, d):
 
 def test_dense_width_limit_is_reported(tw, ctx):
     with pytest.raises(tw.TwtmlError) as e:
-        ctx.batch_from_dense(np.zeros((2, 4096)), np.zeros(2))
+        ctx.batch_from_dense(np.zeros((2, 4097)), np.zeros(2))
     assert e.value.code == tw._lib.E_INVALID_ARG and "CSR" in e.value.message
 
 

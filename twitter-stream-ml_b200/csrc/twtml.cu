@@ -72,11 +72,13 @@ void DevBuf::release()
 int dense_cfg(int64_t d, DenseCfg& c)
 {
     const int64_t ldx = (d + 2) & ~(int64_t)1; // round_up(d + 1, 2)
-    const int64_t c2 = ldx / 2;
+    // column pairs that hold a feature; with d even the (label, pad) pair has no owner thread: only the
+    // per-row threads read it, so narrow even widths (d = 128 -> 64 pairs) fill whole warps
+    const int64_t c2 = (d + 1) / 2;
     if (c2 <= kIterThreads) c.cp = 1;
     else if (c2 <= 2 * kIterThreads) c.cp = 2;
     else if (c2 <= 4 * kIterThreads) c.cp = 4;
-    else return fail(TWTML_E_INVALID_ARG, "dense batches support num_features <= %d; use the CSR form for wider rows", 8 * kIterThreads - 1);
+    else return fail(TWTML_E_INVALID_ARG, "dense batches support num_features <= %d; use the CSR form for wider rows", 8 * kIterThreads);
     c.c2 = (int)c2;
     if (c.cp == 1) {
         c.c2p = (c.c2 + 31) & ~31;
