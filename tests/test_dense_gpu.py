@@ -263,3 +263,29 @@ def test_async_ingest_overlaps_and_matches_sync(tw, ctx, oracle):
     Xp, yp = oracle.synth_dense(100, 8, seed=1)
     b = ctx.batch_from_dense_async(Xp, yp)
     assert b.ready(wait=True) and np.array_equal(b.export_dense()[0], Xp)
+
+
+def test_degenerate_settings_follow_mllib(tw, ctx, oracle):
+    """numIterations = 0 runs nothing; miniBatchFraction <= 0 samples no row, so every iteration sees m = 0:
+    no update, no loss entry (runMiniBatchSGD's `if (miniBatchSize > 0)` branch [U])."""
+    X, y = oracle.synth_dense(500, 16, seed=2)
+    w0 = np.linspace(-1, 1, 16)
+    b = ctx.batch_from_dense(X, y)
+    for iters, frac in [(0, 1.0), (7, 0.0), (7, -0.5)]:
+        m = make_model(tw, ctx, 16, w0, iters=iters, frac=frac)
+        st, _, _ = m.step(b)
+        assert st["batch"] == 500 and len(m.lastLossHistory) == 0
+        assert np.array_equal(m.latestModel().weights.toArray(), w0)
+        w_ref, h_ref = oracle.sgd(y, 16, w0, X=X, num_iterations=iters, mini_batch_fraction=frac, convergence_tol=0.0)
+        assert len(h_ref) == 0 and np.array_equal(w_ref, w0)
+
+
+def test_nonfinite_prediction_is_flagged(tw, ctx):
+    """Utils.round throws NumberFormatException on NaN / Infinity (Utils.scala:4-5): the C ABI counts such rows and
+    the facade raises."""
+    X = np.ones((3, 4))
+    b = ctx.batch_from_dense(X, np.array([1.0, 2.0, 3.0]))
+    m = make_model(tw, ctx, 4, np.array([1e308, 1e308, 1e308, 1e308]))
+    with pytest.raises(ArithmeticError, match="NumberFormatException"):
+        m.predictStats(b)
+    assert m.lastStats["nonfinite"] == 3
