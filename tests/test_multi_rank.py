@@ -83,3 +83,13 @@ def test_two_gpus_match_one_gpu_bit_for_bit(tmp_path):
             assert np.array_equal(outs[1][k], outs[2][k]), k       # same shard vectors, same order, same bits
         else:
             assert np.allclose(outs[1][k], outs[2][k], rtol=1e-9, atol=0)
+
+
+@pytest.mark.gpu
+def test_one_process_one_thread_per_gpu():
+    """The single-JVM shape: ranks are host threads of one process (tools/mgpu_threads_check.py)."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    res = subprocess.run([sys.executable, "tools/mgpu_threads_check.py", "2"], capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert res.returncode == 0 and "THREADS OK 2" in res.stdout, res.stdout[-2000:] + res.stderr[-2000:]
