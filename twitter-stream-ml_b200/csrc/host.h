@@ -50,6 +50,7 @@ struct twtml_ctx {
     ncclComm_t comm = nullptr;
     std::mutex mu;
     int live_handles = 0; // models + batches created on this context and not yet freed
+    unsigned smem_attr_done = 0; // dense iteration-kernel forms whose dynamic shared-memory limit is raised
     // scratch, reused across calls
     twtml::DevBuf partials, shards, stat_partials, stat_shards, state, loss_hist, out10, tmp_a, tmp_b, gather, lower, upd_parts;
     // pinned staging ring for host -> device ingest

@@ -126,11 +126,11 @@ void make_plan(int64_t n_local, int spr, int R, Plan& p)
 template <int CP, int MODE, bool RL1>
 static int launch_iter_t(twtml_ctx* ctx, const DenseCfg& c, const DenseIterArgs& a)
 {
-    static bool attr_set[16] = {false};
     auto kern = k_dense_iter<CP, MODE, RL1>;
-    if (!attr_set[ctx->device & 15]) {
+    constexpr int variant = (CP == 1 ? (RL1 ? 1 : 0) : (CP == 2 ? 2 : 3)) * 4 + MODE; // 16 kernel forms
+    if (!(ctx->smem_attr_done & (1u << variant))) { // once per context (= per device) and kernel form
         TW_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        attr_set[ctx->device & 15] = true;
+        ctx->smem_attr_done |= 1u << variant;
     }
     long long grid = (long long)ctx->sm_count * c.grid_per_sm;
     if (grid > a.plan.nblocks) grid = a.plan.nblocks;
