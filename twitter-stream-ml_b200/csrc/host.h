@@ -50,6 +50,12 @@ struct twtml_ctx {
     ncclComm_t comm = nullptr;
     std::mutex mu;
     int live_handles = 0; // models + batches created on this context and not yet freed
+    // peer-memory exchange of the shard vectors (reduce.cuh PeerExchange); falls back to NCCL when not set up
+    bool p2p_ok = false;
+    double* xbuf = nullptr;                 // this rank's exchange buffer
+    double* peer[twtml::kMaxShards] = {};   // every rank's buffer as mapped here (peer[rank] == xbuf)
+    bool peer_ipc[twtml::kMaxShards] = {};  // mapped with cudaIpcOpenMemHandle (to be closed)
+    unsigned long long xseq = 0;            // exchange sequence number, the same on every rank
     unsigned smem_attr_done = 0; // dense iteration-kernel forms whose dynamic shared-memory limit is raised
     // scratch, reused across calls
     twtml::DevBuf partials, shards, stat_partials, stat_shards, state, loss_hist, out10, tmp_a, tmp_b, gather, lower, upd_parts;

@@ -46,6 +46,72 @@ static __global__ void __launch_bounds__(1024) k_shard_reduce(const double* __re
     }
 }
 
+// ---- exchange of the shard vectors over peer memory (NVLink) ------------------------------------
+// Every rank owns one exchange buffer: data[2 parities][kMaxShards][kPvCap] doubles, then
+// flags[2][kMaxShards] (one per writer rank), then a CTA counter.  All ranks map all buffers (CUDA IPC
+// between processes, direct peer access between threads of one process).  In iteration number seq a
+// rank's k_shard_reduce_p2p stores its shard vectors straight into EVERY rank's buffer (parity seq & 1)
+// and, once its last CTA is done, stores seq into its flag slot on every rank; the update kernel of a
+// rank spins on its own flag slots until all writers have reached seq.  Two parities suffice: nobody
+// can start iteration seq + 2 before every rank has finished reading iteration seq.
+constexpr int kPvCap = 4104;
+constexpr size_t kXbufDataDoubles = (size_t)2 * kMaxShards * kPvCap;
+constexpr size_t kXbufBytes = kXbufDataDoubles * 8 + 2 * kMaxShards * 8 + 64;
+
+struct PeerExchange {
+    double* peer[kMaxShards]; // base of rank r's exchange buffer, as mapped here
+    unsigned* counter;        // local CTA counter
+    int world, rank;
+    unsigned long long seq;
+};
+
+__host__ __device__ __forceinline__ unsigned long long* xbuf_flags(double* base) { return reinterpret_cast<unsigned long long*>(base + kXbufDataDoubles); }
+
+static __global__ void __launch_bounds__(1024) k_shard_reduce_p2p(const double* __restrict__ partials, int pv, Plan plan, PeerExchange px,
+                                                           const TrainState* state)
+{
+    if (state && state->done) return;
+    __shared__ double sm[32][33];
+    const int s = blockIdx.y;
+    const int col = blockIdx.x * 32 + threadIdx.x;
+    const long long b0 = plan.shard_blk0[s], B = plan.shard_blk0[s + 1] - b0;
+    const long long lo = b0 + B * threadIdx.y / 32, hi = b0 + B * (threadIdx.y + 1) / 32;
+    double acc = 0.0;
+    if (col < pv) {
+        long long b = lo;
+        for (; b + 4 <= hi; b += 4) {
+            const double v0 = partials[(b + 0) * pv + col], v1 = partials[(b + 1) * pv + col];
+            const double v2 = partials[(b + 2) * pv + col], v3 = partials[(b + 3) * pv + col];
+            acc += v0;
+            acc += v1;
+            acc += v2;
+            acc += v3;
+        }
+        for (; b < hi; ++b) acc += partials[b * pv + col];
+    }
+    sm[threadIdx.y][threadIdx.x] = acc;
+    __syncthreads();
+    const int parity = (int)(px.seq & 1ull);
+    if (threadIdx.y == 0 && col < pv) {
+        double tot = 0.0;
+#pragma unroll
+        for (int q = 0; q < 32; ++q) tot += sm[q][threadIdx.x];
+        const size_t slot = (size_t)parity * kMaxShards * kPvCap + ((size_t)px.rank * plan.spr + s) * pv + col; // packed nshards x pv like the NCCL path
+        for (int r = 0; r < px.world; ++r) px.peer[r][slot] = tot;
+        __threadfence_system();
+    }
+    __syncthreads();
+    if (threadIdx.x == 0 && threadIdx.y == 0) {
+        const unsigned total = gridDim.x * gridDim.y;
+        if (atomicAdd(px.counter, 1u) == total - 1u) { // last CTA of this rank: everything above is globally visible
+            *px.counter = 0u;
+            __threadfence_system();
+            for (int r = 0; r < px.world; ++r)
+                *reinterpret_cast<volatile unsigned long long*>(xbuf_flags(px.peer[r]) + parity * kMaxShards + px.rank) = px.seq;
+        }
+    }
+}
+
 struct UpdateArgs {
     const double* shards; // nshards x pv   (all ranks' shard vectors, shard order)
     double* w;            // d
@@ -54,7 +120,35 @@ struct UpdateArgs {
     int nshards, pv, d, ldx;
     int max_iter, updater;
     double step, reg, tol;
+    // peer exchange: wait until wait_n writers have stored wait_seq into wait_flags[0..wait_n)
+    const unsigned long long* wait_flags;
+    unsigned long long wait_seq;
+    int wait_n;
 };
+
+constexpr int kPeerTimeoutMark = 0x7E57; // TrainState::pad after a peer never showed up
+
+// returns false when a peer did not arrive within ~10 s (the kernel then stops the training loop)
+__device__ __forceinline__ bool wait_for_peers(const UpdateArgs& a)
+{
+    __shared__ int timed_out;
+    if (!a.wait_flags) return true;
+    if (threadIdx.x == 0) timed_out = 0;
+    __syncthreads();
+    if (threadIdx.x < a.wait_n) {
+        const volatile unsigned long long* f = a.wait_flags + threadIdx.x;
+        const long long t0 = clock64();
+        while (*f < a.wait_seq)
+            if (clock64() - t0 > 20000000000ll) { timed_out = 1; break; }
+    }
+    __syncthreads();
+    __threadfence();
+    if (timed_out) {
+        if (threadIdx.x == 0) { a.state->done = 1; a.state->pad = kPeerTimeoutMark; }
+        return false;
+    }
+    return true;
+}
 
 __device__ __forceinline__ double block_sum_1024(double v, double* sm32)
 {
@@ -130,6 +224,7 @@ static __global__ void __launch_bounds__(1024) k_update(const UpdateArgs a)
 {
     __shared__ double sm32[32];
     if (a.state->done) return;
+    if (!wait_for_peers(a)) return;
     double cnt, loss;
     shard_totals(a, loss, cnt);
     double dn2 = 0.0, wn2 = 0.0, l1 = 0.0;

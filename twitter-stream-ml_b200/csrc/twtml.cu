@@ -9,6 +9,7 @@
 #include <cstring>
 #include <functional>
 #include <thread>
+#include <unistd.h>
 
 #include "dense.cuh"
 #include "host.h"
@@ -174,6 +175,75 @@ static int allgather_inplace(twtml_ctx* ctx, void* buf, size_t count_per_rank, n
     TW_NCCL(nccl_api().AllGather(send, buf, count_per_rank, dt, ctx->comm, ctx->stream));
     ctx->prof.nccl_calls += 1;
     return 0;
+}
+
+// Map every rank's exchange buffer into this rank (collective; all ranks end with the same verdict).
+struct PeerCard {
+    cudaIpcMemHandle_t handle;
+    long long pid;
+    unsigned long long ptr;
+    int dev;
+    int ok;
+};
+
+static int setup_peer_exchange(twtml_ctx* ctx)
+{
+    ctx->p2p_ok = false;
+    const int W = ctx->world;
+    if (W < 2 || W > kMaxShards || kMaxShards % W != 0) return 0;
+    PeerCard mine{};
+    mine.pid = (long long)getpid();
+    mine.dev = ctx->device;
+    mine.ok = 1;
+    if (cudaMalloc(&ctx->xbuf, kXbufBytes) != cudaSuccess || cudaMemset(ctx->xbuf, 0, kXbufBytes) != cudaSuccess ||
+        cudaIpcGetMemHandle(&mine.handle, ctx->xbuf) != cudaSuccess) {
+        cudaGetLastError();
+        mine.ok = 0;
+    }
+    mine.ptr = (unsigned long long)ctx->xbuf;
+    TW_TRY(ctx->gather.reserve(sizeof(PeerCard) * (size_t)W));
+    char* g = ctx->gather.as<char>();
+    TW_CUDA(cudaMemcpyAsync(g + sizeof(PeerCard) * ctx->rank, &mine, sizeof(mine), cudaMemcpyHostToDevice, ctx->stream));
+    TW_TRY(allgather_inplace(ctx, g, sizeof(PeerCard), ncclInt8, 1));
+    std::vector<PeerCard> cards((size_t)W);
+    TW_CUDA(cudaMemcpyAsync(cards.data(), g, sizeof(PeerCard) * (size_t)W, cudaMemcpyDeviceToHost, ctx->stream));
+    TW_CUDA(cudaStreamSynchronize(ctx->stream));
+    int ok = 1;
+    for (int r = 0; r < W; ++r) ok &= cards[r].ok;
+    for (int r = 0; r < W && ok; ++r) {
+        if (r == ctx->rank) { ctx->peer[r] = ctx->xbuf; continue; }
+        if (cards[r].pid == mine.pid) { // another thread of this process: plain peer access
+            int can = 0;
+            cudaDeviceCanAccessPeer(&can, ctx->device, cards[r].dev);
+            cudaError_t e = can ? cudaDeviceEnablePeerAccess(cards[r].dev, 0) : cudaErrorInvalidDevice;
+            if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); e = cudaSuccess; }
+            if (e != cudaSuccess) { cudaGetLastError(); ok = 0; break; }
+            ctx->peer[r] = reinterpret_cast<double*>(cards[r].ptr);
+        } else {
+            void* p = nullptr;
+            if (cudaIpcOpenMemHandle(&p, cards[r].handle, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ok = 0; break; }
+            ctx->peer[r] = static_cast<double*>(p);
+            ctx->peer_ipc[r] = true;
+        }
+    }
+    // second round: a rank that could not map a peer vetoes the scheme for everybody
+    int* flags = reinterpret_cast<int*>(g);
+    TW_CUDA(cudaMemcpyAsync(flags + ctx->rank, &ok, sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    TW_TRY(allgather_inplace(ctx, flags, 1, ncclInt32, sizeof(int)));
+    std::vector<int> oks((size_t)W);
+    TW_CUDA(cudaMemcpyAsync(oks.data(), flags, sizeof(int) * (size_t)W, cudaMemcpyDeviceToHost, ctx->stream));
+    TW_CUDA(cudaStreamSynchronize(ctx->stream));
+    for (int r = 0; r < W; ++r) ok &= oks[r];
+    ctx->p2p_ok = ok != 0 && getenv("TWTML_NO_P2P") == nullptr;
+    return 0;
+}
+
+static void teardown_peer_exchange(twtml_ctx* ctx)
+{
+    for (int r = 0; r < kMaxShards; ++r)
+        if (ctx->peer_ipc[r] && ctx->peer[r]) cudaIpcCloseMemHandle(ctx->peer[r]);
+    if (ctx->xbuf) cudaFree(ctx->xbuf);
+    ctx->xbuf = nullptr;
 }
 
 int ctx_global_rows(twtml_ctx* ctx, int64_t n_local, int64_t* n_global, int64_t* row0)
@@ -382,8 +452,14 @@ static int reserve_scratch(twtml_ctx* ctx, const twtml_model* m, const twtml_bat
 }
 
 // block partials -> shard vectors -> (all-gather) ; leaves every rank with all shard vectors
+static bool use_p2p(const twtml_ctx* ctx, const twtml_batch* b)
+{
+    return ctx->p2p_ok && !b->csr && partial_width(b) <= kPvCap && b->plan.spr * ctx->world <= kMaxShards;
+}
+
 static int exchange_shards(twtml_ctx* ctx, const twtml_batch* b)
 {
+    if (use_p2p(ctx, b)) return 0; // k_shard_reduce_p2p already stored the vectors on every rank
     return allgather_inplace(ctx, ctx->shards.as<double>(), (size_t)b->plan.spr * partial_width(b), ncclDouble, sizeof(double));
 }
 
@@ -394,6 +470,17 @@ static int reduce_local(twtml_ctx* ctx, const twtml_batch* b, bool gated)
     double* mine = ctx->shards.as<double>() + (size_t)ctx->rank * spr * pv;
     if (b->csr) {
         TW_TRY(csr_reduce(ctx, b, mine, gate));
+    } else if (gated && use_p2p(ctx, b)) {
+        PeerExchange px{};
+        for (int r = 0; r < ctx->world; ++r) px.peer[r] = ctx->peer[r];
+        px.counter = reinterpret_cast<unsigned*>(xbuf_flags(ctx->xbuf) + 2 * kMaxShards);
+        px.world = ctx->world;
+        px.rank = ctx->rank;
+        px.seq = ++ctx->xseq;
+        dim3 grid((pv + 31) / 32, spr), block(32, 32);
+        k_shard_reduce_p2p<<<grid, block, 0, ctx->stream>>>(ctx->partials.as<double>(), pv, b->plan, px, gate);
+        TW_CUDA(cudaGetLastError());
+        ctx->prof.other_launches += 1;
     } else {
         dim3 grid((pv + 31) / 32, spr), block(32, 32);
         k_shard_reduce<<<grid, block, 0, ctx->stream>>>(ctx->partials.as<double>(), pv, b->plan, mine, gate);
@@ -512,6 +599,13 @@ static int do_train(twtml_model* m, const twtml_batch* b, bool with_stats, doubl
         TW_TRY(reduce_local(ctx, b, true));
         if (prof && b->csr) TW_CUDA(cudaEventRecord(prof_event(ctx, ne++), ctx->stream));
         TW_TRY(exchange_shards(ctx, b));
+        if (use_p2p(ctx, b)) { // read this iteration's vectors from the local exchange buffer once every writer has signalled
+            const int parity = (int)(ctx->xseq & 1ull);
+            ua.shards = ctx->xbuf + (size_t)parity * kMaxShards * kPvCap;
+            ua.wait_flags = xbuf_flags(ctx->xbuf) + parity * kMaxShards;
+            ua.wait_seq = ctx->xseq;
+            ua.wait_n = ctx->world;
+        }
         if (m->d <= 2 * kWideCols) {
             k_update<<<1, 1024, 0, ctx->stream>>>(ua);
             ctx->prof.other_launches += 1;
@@ -538,6 +632,7 @@ static int do_train(twtml_model* m, const twtml_batch* b, bool with_stats, doubl
         TW_TRY(fetch_rows(ctx, out_real, dr, b->n));
     }
     TW_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (hs.pad == kPeerTimeoutMark) return fail(TWTML_E_NCCL, "peer exchange timed out: a rank never delivered its shard vectors");
     if (with_stats && out) stats_from_out10(o, out);
     if (iters_run) *iters_run = hs.nhist;
     if (loss_history)
@@ -633,6 +728,8 @@ static int32_t create_common(int32_t device, int32_t rank, int32_t world, const 
         memcpy(&uid, id, sizeof(uid));
         ncclResult_t r = nccl_api().CommInitRank(&c->comm, world, uid, rank);
         if (r != ncclSuccess) { delete c; return fail(TWTML_E_NCCL, "ncclCommInitRank: %s", nccl_api().GetErrorString(r)); }
+        int prc = setup_peer_exchange(c);
+        if (prc) { delete c; return prc; }
     }
     *out = c;
     return 0;
@@ -668,6 +765,7 @@ int32_t twtml_destroy(twtml_ctx* ctx)
     }
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    teardown_peer_exchange(ctx);
     if (ctx->comm) nccl_api().CommDestroy(ctx->comm);
     for (DevBuf* b : {&ctx->partials, &ctx->shards, &ctx->stat_partials, &ctx->stat_shards, &ctx->state, &ctx->loss_hist, &ctx->out10,
                       &ctx->tmp_a, &ctx->tmp_b, &ctx->gather, &ctx->lower, &ctx->upd_parts})
