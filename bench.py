@@ -244,6 +244,7 @@ def main():
         kern_ms += p.iter_kernel_ms
         kern_launches += p.iter_launches
         launches += p.iter_launches + p.other_launches
+        nccl_calls = p.nccl_calls
         kbytes = p.iter_kernel_bytes
     barrier()
     wall_ms = (time.perf_counter() - t0) * 1e3
@@ -332,7 +333,9 @@ def main():
                              "kernel": "k_csr_rows + k_csc_windows + k_csc_edges (one read of the CSR credited)" if csr else ("k_dense_iter<1,TRAIN,RL1>" if d + 1 > 992 else "k_dense_iter<1,TRAIN,row lanes>"),
                              "kernel_ms": kern_ms_per_launch, "bytes_per_launch": int(kbytes),
                              "frac_of_nominal_8TBs": achieved / 8000.0},
-                "clocks": clocks, "e2e": e2e, "gpu_launches": launches}
+                "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
+                "exchange": ("none (1 GPU)" if world == 1 else ("NCCL all-gather, %d calls per step" % nccl_calls if nccl_calls else
+                                                                "peer-memory stores + flags inside the reduce/update kernels (0 NCCL calls per step)"))}
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"], _, _ = cpu_leg(wl, 3, 1)
         print(json.dumps(line), flush=True)
