@@ -324,7 +324,7 @@ def main():
                 "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f64", "data": "synthetic",
                 "config": {"workload": args.workload, "rows_per_gpu": n, "features": d, "sgd_iterations": iters,
-                           "convergence_tol": 0.0, **({"tweets_per_gpu": n_tweets, "nnz_per_gpu": batch.nnz} if tweets is not None else {}), "parallelism": "rows sharded x%d, NCCL all-gather of shard partials per iteration" % world,
+                           "convergence_tol": 0.0, **({"tweets_per_gpu": n_tweets, "nnz_per_gpu": batch.nnz} if tweets is not None else {}), "parallelism": "rows sharded x%d, one exchange of the shard partials per iteration" % world,
                            "l2": "inputs (%.2f GB/GPU) larger than L2; no flush needed" % ((batch.nnz * 12 * 2 + n * 24) / 1e9 if csr else n * (d + 2) * 8 / 1e9),
                            "timing": "CUDA events on the library stream around each step's iteration loop, max over ranks"},
                 "wall_ms_per_step": wall_ms / args.steps,

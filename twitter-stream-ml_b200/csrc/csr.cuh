@@ -22,8 +22,7 @@
 
 namespace twtml {
 
-constexpr int kCsrThreads = 256;
-constexpr int kCsrGroups = kCsrThreads / 8; // 8 lanes per row
+constexpr int kCsrThreads = 256; // LPR lanes per row (4 / 8 / 16 by average row length), kCsrThreads / LPR rows at a time
 constexpr int kWin = 256;                   // CSC entries per window (8 head-mask words)
 
 struct CsrIterArgs {
@@ -44,14 +43,15 @@ struct CsrIterArgs {
     int iter_override;
 };
 
-template <int MODE>
+template <int MODE, int LPR>
 __global__ void __launch_bounds__(kCsrThreads) k_csr_rows(const CsrIterArgs a)
 {
+    constexpr int kCsrGroups = kCsrThreads / LPR;
     constexpr bool kTrain = (MODE == MODE_TRAIN || MODE == MODE_TRAIN_STATS);
     constexpr bool kStats = (MODE == MODE_TRAIN_STATS || MODE == MODE_PREDICT_STATS);
     if (kTrain && a.state->done) return;
     __shared__ double sred[kCsrGroups * kStatStride];
-    const int t = threadIdx.x, grp = t >> 3, l8 = t & 7;
+    const int t = threadIdx.x, grp = t / LPR, l8 = t % LPR;
     const unsigned long long iter_seed =
         splitmix64((unsigned long long)(42 + (a.iter_override > 0 ? a.iter_override : (kTrain ? a.state->iter : 0))));
     const bool sampling = kTrain && a.frac < 1.0;
@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(kCsrThreads) k_csr_rows(const CsrIterArgs a)
                 for (int h = 0; h < 2; ++h)
 #pragma unroll
                     for (int u = 0; u < 2; ++u) {
-                        const long long kk = k[h] + 8 * u;
+                        const long long kk = k[h] + LPR * u;
                         const bool p = kk < e[h];
                         ci[h][u] = p ? a.colidx[kk] : 0;
                         vv[h][u] = p ? a.vals[kk] : 0.0;
@@ -97,9 +97,9 @@ __global__ void __launch_bounds__(kCsrThreads) k_csr_rows(const CsrIterArgs a)
                     for (int u = 0; u < 2; ++u) ww[h][u] = a.w[ci[h][u]];
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
-                    accs[h] = fma(vv[h][0], ww[h][0], accs[h]); // entries k, k+8, k+16, ... in this order per lane
+                    accs[h] = fma(vv[h][0], ww[h][0], accs[h]); // entries k, k+LPR, k+2 LPR, ... in this order per lane
                     accs[h] = fma(vv[h][1], ww[h][1], accs[h]);
-                    k[h] += 16;
+                    k[h] += 2 * LPR;
                 }
             }
           }
@@ -109,9 +109,8 @@ __global__ void __launch_bounds__(kCsrThreads) k_csr_rows(const CsrIterArgs a)
             const bool valid = valids[h];
             const long long row = row0 + r;
             double acc = accs[h];
-            acc += shfl_xor_f64(acc, 4);
-            acc += shfl_xor_f64(acc, 2);
-            acc += shfl_xor_f64(acc, 1);
+#pragma unroll
+            for (int mk = LPR / 2; mk >= 1; mk >>= 1) acc += shfl_xor_f64(acc, mk);
             if (valid && l8 == 0) {
                 const double y = a.labels[row];
                 if (kTrain) {

@@ -111,7 +111,7 @@ namespace twtml {
 // shared between twtml.cu and twtml_sparse.cu
 int upload_plain(twtml_ctx* ctx, void* dst, const void* src, size_t bytes);
 int ctx_global_rows(twtml_ctx* ctx, int64_t n_local, int64_t* n_global, int64_t* row0);
-void make_plan(int64_t n_local, int spr, int R, Plan& p);
+void make_plan(int64_t n_local, int spr, int R, Plan& p, int64_t min_blocks = 64);
 void batch_free_locked(twtml_batch* b);
 // batch memory from the context's pool, ordered on the compute stream
 int pool_alloc(twtml_ctx* ctx, void** p, size_t bytes);

@@ -99,13 +99,13 @@ int dense_cfg(int64_t d, DenseCfg& c)
     return 0;
 }
 
-void make_plan(int64_t n_local, int spr, int R, Plan& p)
+void make_plan(int64_t n_local, int spr, int R, Plan& p, int64_t min_blocks)
 {
     memset(&p, 0, sizeof(p));
     p.spr = spr;
     const int64_t nominal = (n_local + spr - 1) / spr;
     int64_t rb = 512;
-    while (rb > 1 && rb * 64 > nominal) rb >>= 1;
+    while (rb > 1 && rb * min_blocks > nominal) rb >>= 1; // a function of the row count only: keeps results grid-independent
     rb = std::max<int64_t>(1, rb / R) * R;
     p.rb = (int)rb;
     long long blk = 0;

@@ -42,7 +42,9 @@ static unsigned blocks_for(long long n, int threads) { return (unsigned)std::max
 // rowptr / colidx / vals / labels are on the device: build the plan, the transpose and the column tasks
 static int csr_finalize(twtml_ctx* ctx, twtml_batch* b)
 {
-    make_plan(b->n, 1, 1, b->plan); // one shard per rank: the column sums are per rank, not per virtual shard
+    // one shard per rank (the column sums are per rank, not per virtual shard); row blocks small enough to give every SM
+    // several CTAs of the row pass even for a modest micro-batch (but at least 32 rows: one step of the widest row form)
+    make_plan(b->n, 1, 32, b->plan, 4096);
     TW_TRY(ctx_global_rows(ctx, b->n, &b->n_global, &b->row0_global));
     if (b->nnz >= ((long long)1 << 31) || b->n >= ((long long)1 << 31))
         return fail(TWTML_E_INVALID_ARG, "CSR batch too large for 32-bit entry indices (%lld rows, %lld nnz per GPU)", (long long)b->n, (long long)b->nnz);
@@ -148,14 +150,22 @@ int csr_launch_iter(twtml_ctx* ctx, const twtml_model* m, const twtml_batch* b, 
     a.frac = m->frac;
     a.row0_global = (unsigned long long)b->row0_global;
     a.iter_override = iter_override;
-    const unsigned grid = (unsigned)std::min<long long>(b->plan.nblocks, (long long)ctx->sm_count * 8);
+    const unsigned grid = (unsigned)std::min<long long>(b->plan.nblocks, (long long)ctx->sm_count * 16);
     if (grid == 0) return 0;
+    const double avg = b->n > 0 ? (double)b->nnz / (double)b->n : 0.0; // lanes per row follow the average row length
+#define TW_ROWS(MODE_)                                                                        \
+    do {                                                                                      \
+        if (avg <= 12.0) k_csr_rows<MODE_, 4><<<grid, kCsrThreads, 0, ctx->stream>>>(a);      \
+        else if (avg <= 48.0) k_csr_rows<MODE_, 8><<<grid, kCsrThreads, 0, ctx->stream>>>(a); \
+        else k_csr_rows<MODE_, 16><<<grid, kCsrThreads, 0, ctx->stream>>>(a);                 \
+    } while (0)
     switch (mode) {
-    case MODE_TRAIN: k_csr_rows<MODE_TRAIN><<<grid, kCsrThreads, 0, ctx->stream>>>(a); break;
-    case MODE_TRAIN_STATS: k_csr_rows<MODE_TRAIN_STATS><<<grid, kCsrThreads, 0, ctx->stream>>>(a); break;
-    case MODE_PREDICT: k_csr_rows<MODE_PREDICT><<<grid, kCsrThreads, 0, ctx->stream>>>(a); break;
-    default: k_csr_rows<MODE_PREDICT_STATS><<<grid, kCsrThreads, 0, ctx->stream>>>(a); break;
+    case MODE_TRAIN: TW_ROWS(MODE_TRAIN); break;
+    case MODE_TRAIN_STATS: TW_ROWS(MODE_TRAIN_STATS); break;
+    case MODE_PREDICT: TW_ROWS(MODE_PREDICT); break;
+    default: TW_ROWS(MODE_PREDICT_STATS); break;
     }
+#undef TW_ROWS
     TW_CUDA(cudaGetLastError());
     return 0;
 }
