@@ -112,6 +112,21 @@ static __global__ void __launch_bounds__(1024) k_shard_reduce_p2p(const double* 
     }
 }
 
+// (lossSum, count) pairs of the CSR row blocks -> out[0..1]; one CTA: 1024 slices in block order, then a fixed tree
+__device__ __forceinline__ double block_sum_1024(double v, double* sm32);
+static __global__ void __launch_bounds__(1024) k_pair_reduce(const double* __restrict__ pairs, long long nb, double* __restrict__ out,
+                                                      const TrainState* gate)
+{
+    __shared__ double sm32[32];
+    if (gate && gate->done) return;
+    const long long lo = nb * threadIdx.x / 1024, hi = nb * (threadIdx.x + 1) / 1024;
+    double a = 0.0, c = 0.0;
+    for (long long b = lo; b < hi; ++b) { a += pairs[2 * b]; c += pairs[2 * b + 1]; }
+    a = block_sum_1024(a, sm32);
+    c = block_sum_1024(c, sm32);
+    if (threadIdx.x == 0) { out[0] = a; out[1] = c; }
+}
+
 struct UpdateArgs {
     const double* shards; // nshards x pv   (all ranks' shard vectors, shard order)
     double* w;            // d

@@ -183,8 +183,7 @@ int csr_reduce(twtml_ctx* ctx, const twtml_batch* b, double* shard_out, const Tr
         const unsigned g2 = (unsigned)std::min<long long>((b->nwin + 255) / 256, (long long)ctx->sm_count * 32);
         k_csc_edges<<<g2, 256, 0, ctx->stream>>>(c, b->win_first_part, b->win_last_part, shard_out, gate);
     }
-    dim3 grid(1, 1), block(32, 32);
-    k_shard_reduce<<<grid, block, 0, ctx->stream>>>(ctx->partials.as<double>(), 2, b->plan, shard_out + d, gate);
+    k_pair_reduce<<<1, 1024, 0, ctx->stream>>>(ctx->partials.as<double>(), b->plan.nblocks, shard_out + d, gate);
     TW_CUDA(cudaGetLastError());
     ctx->prof.other_launches += 3;
     return 0;
