@@ -56,6 +56,8 @@ struct twtml_ctx {
     double* peer[twtml::kMaxShards] = {};   // every rank's buffer as mapped here (peer[rank] == xbuf)
     bool peer_ipc[twtml::kMaxShards] = {};  // mapped with cudaIpcOpenMemHandle (to be closed)
     unsigned long long xseq = 0;            // exchange sequence number, the same on every rank
+    int* host_done = nullptr;     // mapped pinned word: the update kernel sets it when a training loop has ended
+    int* host_done_dev = nullptr; // ... its device alias
     unsigned smem_attr_done = 0; // dense iteration-kernel forms whose dynamic shared-memory limit is raised
     // scratch, reused across calls
     twtml::DevBuf partials, shards, stat_partials, stat_shards, state, loss_hist, out10, tmp_a, tmp_b, gather, lower, upd_parts;

@@ -139,6 +139,7 @@ struct UpdateArgs {
     const unsigned long long* wait_flags;
     unsigned long long wait_seq;
     int wait_n;
+    int* host_done; // mapped host word set when the loop is over, so a single-GPU host can stop enqueuing no-op iterations
 };
 
 constexpr int kPeerTimeoutMark = 0x7E57; // TrainState::pad after a peer never showed up
@@ -231,7 +232,10 @@ __device__ __forceinline__ void finish_iteration(const UpdateArgs& a, double los
     }
     st->last_count = cnt;
     st->iter = i + 1;
-    if (converged || i + 1 > a.max_iter) st->done = 1;
+    if (converged || i + 1 > a.max_iter) {
+        st->done = 1;
+        if (a.host_done) { *reinterpret_cast<volatile int*>(a.host_done) = 1; __threadfence_system(); }
+    }
 }
 
 // Narrow models (the dense path): one CTA of 1024 threads does the whole update.

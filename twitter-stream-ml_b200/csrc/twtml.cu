@@ -585,11 +585,18 @@ static int do_train(twtml_model* m, const twtml_batch* b, bool with_stats, doubl
     ua.step = m->step;
     ua.reg = m->reg;
     ua.tol = m->tol;
+    // One GPU: the host may stop enqueuing once the device has flagged the end of the loop (converged early);
+    // with several ranks every rank must issue the same sequence of exchanges, so all iterations are enqueued.
+    const bool may_stop_early = ctx->world == 1 && ctx->host_done_dev != nullptr;
+    if (may_stop_early) { *ctx->host_done = 0; ua.host_done = ctx->host_done_dev; }
 
     const bool prof = ctx->profiling;
     size_t ne = 0;
     if (prof) TW_CUDA(cudaEventRecord(prof_event(ctx, ne++), ctx->stream));
+    int enqueued = 0;
     for (int i = 1; i <= m->num_iter; ++i) {
+        if (may_stop_early && i > 2 && *reinterpret_cast<volatile int*>(ctx->host_done)) break;
+        ++enqueued;
         const int mode = (i == 1 && with_stats) ? MODE_TRAIN_STATS : MODE_TRAIN;
         if (prof) TW_CUDA(cudaEventRecord(prof_event(ctx, ne++), ctx->stream));
         TW_TRY(run_pass(ctx, m, b, mode, dp, dr, 0));
@@ -639,7 +646,7 @@ static int do_train(twtml_model* m, const twtml_batch* b, bool with_stats, doubl
         for (int i = 0; i < hs.nhist && i < cap; ++i) loss_history[i] = hist[i];
     if (prof) {
         float ms = 0.f, tot = 0.f;
-        for (int i = 0; i < m->num_iter; ++i) {
+        for (int i = 0; i < enqueued; ++i) {
             cudaEventElapsedTime(&ms, ctx->ev[1 + 2 * i], ctx->ev[2 + 2 * i]);
             tot += ms;
         }
@@ -722,6 +729,11 @@ static int32_t create_common(int32_t device, int32_t rank, int32_t world, const 
         cudaMemPoolSetAttribute(c->pool, cudaMemPoolAttrReleaseThreshold, &keep);
     }
     for (int i = 0; i < 2; ++i) cudaEventCreateWithFlags(&c->pin_ev[i], cudaEventDisableTiming);
+    if (cudaHostAlloc(reinterpret_cast<void**>(&c->host_done), sizeof(int), cudaHostAllocMapped) == cudaSuccess) {
+        *c->host_done = 0;
+        if (cudaHostGetDevicePointer(reinterpret_cast<void**>(&c->host_done_dev), c->host_done, 0) != cudaSuccess) c->host_done_dev = nullptr;
+    }
+    cudaGetLastError();
     if (world > 1) {
         if (!nccl_api().ok) { delete c; return fail(TWTML_E_NCCL, "libnccl.so.2 could not be loaded: %s", dlerror()); }
         ncclUniqueId uid;
@@ -766,6 +778,7 @@ int32_t twtml_destroy(twtml_ctx* ctx)
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     teardown_peer_exchange(ctx);
+    if (ctx->host_done) cudaFreeHost(ctx->host_done);
     if (ctx->comm) nccl_api().CommDestroy(ctx->comm);
     for (DevBuf* b : {&ctx->partials, &ctx->shards, &ctx->stat_partials, &ctx->stat_shards, &ctx->state, &ctx->loss_hist, &ctx->out10,
                       &ctx->tmp_a, &ctx->tmp_b, &ctx->gather, &ctx->lower, &ctx->upd_parts})
