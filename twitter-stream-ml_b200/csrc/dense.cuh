@@ -94,14 +94,15 @@ struct IterSmem {
     static constexpr unsigned kBars = 0;                        // 8 x u64
     static constexpr unsigned kWpart = 64;                      // kIterWarps x 4 doubles
     static constexpr unsigned kDiff = kWpart + kIterWarps * 4 * 8; // 64 doubles
-    static constexpr unsigned kRed = kDiff + 64 * 8;            // 64 x kStatStride doubles (loss/count/stats flush)
-    static constexpr unsigned kGbuf = kRed + 64 * kStatStride * 8; // kIterThreads x 2 doubles
-    static constexpr unsigned kStages = ((kGbuf + kIterThreads * 16) + 127) & ~127u;
+    static constexpr unsigned kRed = kDiff + 64 * 8;            // 64 x (lossSum, count) of the per-row threads at a block's end
+    static constexpr unsigned kGbuf = kRed + 64 * 2 * 8;        // kIterThreads x 2 doubles (row-lane fold)
+    static constexpr unsigned kStat = kGbuf + kIterThreads * 16;  // 64 x kStatStride doubles: the per-row threads' StatCounter tuples
+    static constexpr unsigned kStages = ((kStat + 64 * kStatStride * 8) + 127) & ~127u;
 };
 
 // RL1: one row lane (c2p == 512 or CP > 1): the common wide-row case, with compile-time offsets.
 template <int CP, int MODE, bool RL1>
-__global__ void __launch_bounds__(kIterThreads, (CP == 1 && (MODE == MODE_TRAIN || MODE == MODE_PREDICT)) ? 2 : 1) k_dense_iter(const DenseIterArgs a)
+__global__ void __launch_bounds__(kIterThreads, (CP == 1) ? 2 : 1) k_dense_iter(const DenseIterArgs a)
 {
     constexpr bool kTrain = (MODE == MODE_TRAIN || MODE == MODE_TRAIN_STATS);
     constexpr bool kStats = (MODE == MODE_TRAIN_STATS || MODE == MODE_PREDICT_STATS);
@@ -115,6 +116,7 @@ __global__ void __launch_bounds__(kIterThreads, (CP == 1 && (MODE == MODE_TRAIN 
     double* sdiff = reinterpret_cast<double*>(smem + IterSmem::kDiff);
     double* sred = reinterpret_cast<double*>(smem + IterSmem::kRed);
     double* gbuf = reinterpret_cast<double*>(smem + IterSmem::kGbuf);
+    double* sstat = reinterpret_cast<double*>(smem + IterSmem::kStat); // kept in shared memory: only R threads use them, registers are per thread
     unsigned char* stages = smem + IterSmem::kStages;
 
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
@@ -153,6 +155,8 @@ __global__ void __launch_bounds__(kIterThreads, (CP == 1 && (MODE == MODE_TRAIN 
     // rows beyond a ragged stage's end are read as whatever the slot held before: make that finite
     for (unsigned o = (unsigned)t * 16; o < (unsigned)S * a.stage_stride; o += kIterThreads * 16)
         *reinterpret_cast<double2*>(stages + o) = make_double2(0.0, 0.0);
+    if (kStats && t < 64)
+        for (int q = 0; q < kStatStride; ++q) sstat[t * kStatStride + q] = 0.0;
     if (t == 0) {
         for (int s = 0; s < S; ++s) mbar_init(&full[s], 1);
         mbar_fence_init();
@@ -184,8 +188,6 @@ __global__ void __launch_bounds__(kIterThreads, (CP == 1 && (MODE == MODE_TRAIN 
 #pragma unroll
     for (int p = 0; p < CP; ++p) g0[p] = g1[p] = 0.0;
     double my_loss = 0.0, my_cnt = 0.0; // threads t < R: their row of every stage
-    Stat7 my_stat;
-    stat_zero(my_stat);
     // thread t < R finishes row t of each stage: that is row lane t % RL, k-th row t / RL
     const double* my_wpart = wpart + ((RL1 ? 0 : (t % RL) * wpr) * 4 + (RL1 ? t : t / RL));
     const unsigned yoff = (unsigned)(((long long)t * ldx + d) * 8);
@@ -244,7 +246,10 @@ __global__ void __launch_bounds__(kIterThreads, (CP == 1 && (MODE == MODE_TRAIN 
                     }
                     if (kStats) {
                         const double pr = round_half_up(dot + 0.0);
-                        stat_add(my_stat, y, pr);
+                        Stat7 ms;
+                        stat_load(ms, sstat + t * kStatStride);
+                        stat_add(ms, y, pr);
+                        stat_store(sstat + t * kStatStride, ms);
                         if (a.out_pred) a.out_pred[lrow] = pr;
                         if (a.out_real) a.out_real[lrow] = y;
                     } else if (MODE == MODE_PREDICT) {
@@ -313,20 +318,20 @@ __global__ void __launch_bounds__(kIterThreads, (CP == 1 && (MODE == MODE_TRAIN 
             if (kStats || !RL1) __syncthreads(); // sred / gbuf are reused below / by the next block
         }
         if (kStats) {
-            if (t < R) stat_store(sred + t * kStatStride, my_stat);
             __syncthreads();
             if (t == 0) {
                 Stat7 acc;
                 stat_zero(acc);
                 for (int q = 0; q < R; ++q) {
                     Stat7 s;
-                    stat_load(s, sred + q * kStatStride);
+                    stat_load(s, sstat + q * kStatStride);
                     stat_merge(acc, s);
                 }
                 stat_store(a.stat_partials + blk * kStatStride, acc);
             }
-            stat_zero(my_stat);
             __syncthreads();
+            if (t < R)
+                for (int q = 0; q < kStatStride; ++q) sstat[t * kStatStride + q] = 0.0;
         }
     }
 }
