@@ -37,7 +37,10 @@ WORKLOADS = {
     # configs[4] per GPU: 2^21 rows (2^24 over 8 GPUs), 2^20 hashed + 4 numeric columns, ~24 nnz/row, uniform columns
     "csr_2m": dict(rows=1 << 21, d=(1 << 20) + 4, d_text=1 << 20, iters=50, step=0.005, csr=True),
 }
-WORKLOADS["tweets_1m"] = dict(rows=1000000, d=1004, iters=50, step=0.005, csr=True, tweets=True)
+WORKLOADS["tweets_1m"] = dict(rows=1000000, d=1004, iters=50, step=0.005, csr=True, tweets=True, buckets=1000)
+# configs[4], distribution A: the same tweets hashed into 2^20 buckets -- char bigrams of mostly-ASCII text land in a few
+# thousand of them, i.e. extreme column skew
+WORKLOADS["tweets_1m_wide"] = dict(rows=1000000, d=(1 << 20) + 4, iters=50, step=0.005, csr=True, tweets=True, buckets=1 << 20)
 METRIC = "sgd_row_iterations_per_s"
 UNIT = "row*iter/s"
 
@@ -221,7 +224,7 @@ def main():
     if wl.get("tweets"):
         cols, now_ms = synth_tweets(n, 20160601 + rank)
         tweets = tw.TweetBatch.from_arrays(**cols)
-        batch = ctx.batch_from_tweets(tweets, now_ms)                # filter + featurise on the GPU
+        batch = ctx.batch_from_tweets(tweets, now_ms, 100, 1000, wl["buckets"])   # filter + featurise on the GPU
         n_tweets, n = n, batch.n                                     # the metric counts the rows that train
     elif csr:
         batch = ctx.batch_synth_csr(n, wl["d_text"], seed=42, row0=rank * n)
@@ -261,7 +264,7 @@ def main():
         if tweets is not None:
             h2d = sum(getattr(tweets, k).nbytes for k in ("text_utf16", "text_off", "retweet_count", "followers", "favourites",
                                                            "friends", "created_ms", "is_retweet"))
-            make = lambda: ctx.batch_from_tweets(tweets, now_ms)
+            make = lambda: ctx.batch_from_tweets(tweets, now_ms, 100, 1000, wl["buckets"])
         elif csr:
             host = batch.export_csr()                                  # host copy of this rank's rows
             h2d = sum(a.nbytes for a in host)
