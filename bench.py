@@ -115,32 +115,56 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-def cpu_leg(wl, steps, warmup, budget_s=15.0):
+def cpu_leg(wl, steps, warmup, budget_s=15.0, threads=None):
     """The CPU restatement (oracle/twtml_oracle.c, OpenMP over row partitions like Spark local[N]) on a
-    bounded sample of the workload: same width, same iteration count, fewer rows."""
+    bounded sample of the workload: same width, same iteration count, fewer rows (dense: 2^17 rows;
+    CSR: 2^18 rows; tweets: 10^5 tweets, featurised by the restatement inside the timed step)."""
     from oracle import oracle_c
     import numpy as np
     oracle_c.build()
-    cores = oracle_c.max_threads()
+    cores = threads or oracle_c.max_threads()
     d, iters = wl["d"], wl["iters"]
-    rows = 1 << 17
-    X, y = oracle_c.synth_dense(rows, d, seed=42)
     w0 = np.zeros(d)
-    kw = dict(X=X, step_size=wl["step"], num_iterations=iters, convergence_tol=0.0, partitions=cores, threads=cores)
+    common = dict(step_size=wl["step"], num_iterations=iters, convergence_tol=0.0, partitions=cores, threads=cores)
+    if wl.get("tweets"):
+        n_t = 100000
+        cols, now = synth_tweets(n_t, 20160601)
+        c = {k: np.ascontiguousarray(v) for k, v in cols.items()}
+
+        def step():
+            rp, ci, va, la = oracle_c.featurize(c["text_utf16"], c["text_off"], c["retweet_count"], c["followers"], c["favourites"],
+                                                c["friends"], c["created_ms"], c["is_retweet"].astype(np.uint8), now, 100, 1000, wl["buckets"])
+            oracle_c.sgd(la, d, w0, csr=(rp, ci, va), **common)
+            return len(la)
+        what = "%d of %d tweets (featuriser + %d iterations on the rows that pass the filter)" % (n_t, wl["rows"], iters)
+    elif wl.get("csr"):
+        rows = 1 << 18
+        rp, ci, va, la = oracle_c.synth_csr(rows, wl["d_text"], seed=42)
+
+        def step():
+            oracle_c.sgd(la, d, w0, csr=(rp, ci, va), **common)
+            return rows
+        what = "%d of %d rows x %d columns CSR, %d iterations" % (rows, wl["rows"], d, iters)
+    else:
+        rows = 1 << 17
+        X, y = oracle_c.synth_dense(rows, d, seed=42)
+
+        def step():
+            oracle_c.sgd(y, d, w0, X=X, **common)
+            return rows
+        what = "%d of %d rows x %d features, %d iterations" % (rows, wl["rows"], d, iters)
     t0 = time.perf_counter()
-    oracle_c.sgd(y, d, w0, **kw)                       # also the first warm-up step
+    step()                                              # also the first warm-up step
     once = time.perf_counter() - t0
-    warm = max(0, warmup - 1)
     k = max(1, min(steps, int(budget_s / max(once, 1e-3))))
-    for _ in range(min(warm, 2)):
-        oracle_c.sgd(y, d, w0, **kw)
+    for _ in range(min(max(0, warmup - 1), 2)):
+        step()
     t0 = time.perf_counter()
     for _ in range(k):
-        oracle_c.sgd(y, d, w0, **kw)
+        units = step()
     dt = time.perf_counter() - t0
-    value = rows * iters * k / dt
-    sample = "%d of %d rows x %d features, %d iterations, %d steps, OpenMP static row partitions on %d threads" % (
-        rows, wl["rows"], d, iters, k, cores)
+    value = units * iters * k / dt
+    sample = "%s, %d steps, OpenMP static row partitions on %d threads" % (what, k, cores)
     return dict(value=value, unit=UNIT, cores=cores, kind="port", sample=sample), dt / k * 1e3, k
 
 
@@ -149,12 +173,14 @@ def run_reference(args, wl):
     if rank != 0:
         return
     cb, ms, k = cpu_leg(wl, args.steps, args.warmup)
+    cb2, _, _ = cpu_leg(wl, 2, 1, budget_s=8.0, threads=2)            # README.md:55 of the reference: --master local[2]
     line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": k,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
             "config": {"workload": args.workload, "rows_per_gpu": wl["rows"], "features": wl["d"], "sgd_iterations": wl["iters"],
                        "note": "CPU restatement of the reference's MLlib 1.6.1 path (the Scala/Spark reference cannot run here: no JVM)"},
-            "cpu_baseline": cb, "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "cpu_baseline": cb, "cpu_baseline_local2": cb2,
+            "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
 
