@@ -61,3 +61,11 @@ def test_product_never_touches_the_oracle():
         for f in files:
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 assert not bad.search(open(os.path.join(dp, f)).read()), f
+
+
+def test_stats_wire_format_matches_the_web_client():
+    """web/src/test/.../WebTestSuite.scala:10-11 uses Stats(1000, 10, 2000, 15, 25); web/src/main/assets/js/api.js:55-63
+    reads count / batch / mse / realStddev / predStddev from the same JSON."""
+    import json
+    body = twtml_b200.stats_payload(1000, dict(batch=10, mse=2000.0, real_stdev=15.0, pred_stdev=25.0))
+    assert json.loads(body) == {"jsonClass": "Stats", "count": 1000, "batch": 10, "mse": 2000, "realStddev": 15, "predStddev": 25}

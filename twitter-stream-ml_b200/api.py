@@ -454,6 +454,15 @@ class StreamingLinearRegressionWithSGD:
         return stream.map(f)
 
 
+def stats_payload(count, stats):
+    """The JSON body SessionStats.update posts to twtml-web for one batch (SessionStats.scala:22-33 ->
+    web/WebClient.scala:21-38, ApiTypes.scala:5-17; json4s ShortTypeHints put the class name under "jsonClass"):
+    all five numbers are Longs -- the already Utils.round-ed statistics truncated with .toLong."""
+    import json
+    return json.dumps({"jsonClass": "Stats", "count": int(count), "batch": int(stats["batch"]), "mse": int(stats["mse"]),
+                       "realStddev": int(stats["real_stdev"]), "predStddev": int(stats["pred_stdev"])}, separators=(",", ":"))
+
+
 def _is_empty(rdd):
     return rdd.isEmpty() if isinstance(rdd, Batch) else len(rdd) == 0
 
