@@ -55,6 +55,20 @@ def main():
             ms.trainOnBatch(bs)
             ws_ref, hs_ref = oracle_c.sgd(la, 504, np.zeros(504), csr=(rp, ci, va), step_size=0.005, num_iterations=6, convergence_tol=0.0)
             assert np.max(np.abs(ms.latestModel().weights.toArray() - ws_ref)) / np.max(np.abs(ws_ref)) < 1e-6
+            # a wide hashed model takes the sliced exchange (all-to-all of gradient slices, sliced update, all-gather of w)
+            dw = 20000 + 4
+            rp, ci, va, la = oracle_c.synth_csr(n, 20000, seed=10)
+            mw = (tw.StreamingLinearRegressionWithSGD(ctx=ctx).setNumIterations(6).setStepSize(0.005)
+                  .setInitialWeights(tw.Vectors.zeros(dw)))                      # default tolerance: may stop early
+            bw = ctx.batch_from_csr(hi - lo, dw, rp[lo:hi + 1] - rp[lo], ci[rp[lo]:rp[hi]], va[rp[lo]:rp[hi]], la[lo:hi])
+            stw, _, _ = mw.step(bw)
+            ww_ref, hw_ref = oracle_c.sgd(la, dw, np.zeros(dw), csr=(rp, ci, va), step_size=0.005, num_iterations=6)
+            ww = mw.latestModel().weights.toArray()
+            assert len(mw.lastLossHistory) == len(hw_ref) and stw["batch"] == n
+            assert np.max(np.abs(ww - ww_ref)) / np.max(np.abs(ww_ref)) < 1e-6
+            assert np.max(np.abs(mw.lastLossHistory - hw_ref) / np.abs(hw_ref)) < 1e-6
+            wt2 = torch.from_numpy(ww).cuda(); w0t2 = wt2.clone(); dist.broadcast(w0t2, src=0)
+            assert torch.equal(wt2, w0t2), "ranks disagree on the wide weights"
     if rank == 0:
         np.savez(os.environ.get("MGPU_OUT", "/tmp/mgpu_w%d.npz" % world), **{"%d_%d" % k: v for k, v in results.items()})
         print("MGPU OK world=%d" % world, flush=True)

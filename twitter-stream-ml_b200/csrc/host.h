@@ -60,7 +60,7 @@ struct twtml_ctx {
     int* host_done_dev = nullptr; // ... its device alias
     unsigned smem_attr_done = 0; // dense iteration-kernel forms whose dynamic shared-memory limit is raised
     // scratch, reused across calls
-    twtml::DevBuf partials, shards, stat_partials, stat_shards, state, loss_hist, out10, tmp_a, tmp_b, gather, lower, upd_parts;
+    twtml::DevBuf partials, shards, stat_partials, stat_shards, state, loss_hist, out10, tmp_a, tmp_b, gather, lower, upd_parts, slices, wprev;
     // pinned staging ring for host -> device ingest
     void* pin[2] = {nullptr, nullptr};
     size_t pin_bytes = 0;

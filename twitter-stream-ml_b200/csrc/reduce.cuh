@@ -279,6 +279,86 @@ static __global__ void __launch_bounds__(1024) k_update_wide(const UpdateArgs a,
     if (threadIdx.x == 0) { part[blockIdx.x * 3] = dn2; part[blockIdx.x * 3 + 1] = wn2; part[blockIdx.x * 3 + 2] = l1; }
 }
 
+// ---- wide models on several ranks: every rank owns a slice of the columns ------------------------
+// After an all-to-all of gradient slices (NCCL send/recv; pure data movement), rank r holds, for its own
+// columns [lo, hi), the W partial sums in rank order: it adds them in that order, updates its slice of w,
+// and an all-gather hands every rank the whole new w.  Each rank then computes the two norms of
+// isConverged [U] over all columns itself (same data, same kernel: same bits everywhere).
+struct SliceArgs {
+    const double* slices; // W x slice_len: rank r's sums for my columns at slices + r * slice_len
+    const double* pairs;  // W x 2: every rank's (lossSum, count)
+    double* w;
+    const TrainState* state;
+    int W, slice_len, lo, hi;
+    int updater;
+    double step, reg;
+};
+
+static __global__ void __launch_bounds__(1024) k_update_slice(const SliceArgs a)
+{
+    if (a.state->done) return;
+    double cnt = 0.0;
+    for (int r = 0; r < a.W; ++r) cnt += a.pairs[2 * r + 1];
+    if (!(cnt > 0.0)) return;
+    const double this_step = a.step / sqrt((double)a.state->iter);
+    const int j0 = a.lo + blockIdx.x * kWideCols, j1 = min(a.hi, j0 + kWideCols);
+    for (int j = j0 + threadIdx.x; j < j1; j += blockDim.x) {
+        double g = 0.0;
+        for (int r = 0; r < a.W; ++r) g += a.slices[(long long)r * a.slice_len + (j - a.lo)];
+        g = g / cnt;
+        const double wo = a.w[j];
+        double wn;
+        if (a.updater == 1) {
+            wn = __dmul_rn(wo, 1.0 - this_step * a.reg);
+            wn = __dadd_rn(wn, __dmul_rn(-this_step, g));
+        } else {
+            wn = __dadd_rn(wo, __dmul_rn(-this_step, g));
+            if (a.updater == 2) {
+                const double shr = a.reg * this_step;
+                const double m = fabs(wn) - shr;
+                const double sg = (double)((wn > 0.0) - (wn < 0.0));
+                wn = sg * (m > 0.0 ? m : 0.0);
+            }
+        }
+        a.w[j] = wn;
+    }
+}
+
+// per-CTA partials of ||w_prev - w||^2, ||w||^2, ||w||_1 over kWideCols columns each
+static __global__ void __launch_bounds__(1024) k_norms_wide(const double* __restrict__ w, const double* __restrict__ wprev, int d,
+                                                     const TrainState* state, double* __restrict__ part)
+{
+    __shared__ double sm32[32];
+    if (state->done) return;
+    double dn2 = 0.0, wn2 = 0.0, l1 = 0.0;
+    const int lo = blockIdx.x * kWideCols, hi = min(d, lo + kWideCols);
+    for (int j = lo + threadIdx.x; j < hi; j += blockDim.x) {
+        const double wn = w[j], df = wprev[j] - wn;
+        dn2 += df * df;
+        wn2 += wn * wn;
+        l1 += fabs(wn);
+    }
+    dn2 = block_sum_1024(dn2, sm32);
+    wn2 = block_sum_1024(wn2, sm32);
+    l1 = block_sum_1024(l1, sm32);
+    if (threadIdx.x == 0) { part[blockIdx.x * 3] = dn2; part[blockIdx.x * 3 + 1] = wn2; part[blockIdx.x * 3 + 2] = l1; }
+}
+
+static __global__ void __launch_bounds__(1024) k_slice_finish(const UpdateArgs a, const double* __restrict__ pairs, int W,
+                                                       const double* __restrict__ part, int nparts)
+{
+    __shared__ double sm32[32];
+    if (a.state->done) return;
+    double loss = 0.0, cnt = 0.0;
+    for (int r = 0; r < W; ++r) { loss += pairs[2 * r]; cnt += pairs[2 * r + 1]; }
+    double dn2 = 0.0, wn2 = 0.0, l1 = 0.0;
+    for (int p = threadIdx.x; p < nparts; p += blockDim.x) { dn2 += part[p * 3]; wn2 += part[p * 3 + 1]; l1 += part[p * 3 + 2]; }
+    dn2 = block_sum_1024(dn2, sm32);
+    wn2 = block_sum_1024(wn2, sm32);
+    l1 = block_sum_1024(l1, sm32);
+    if (threadIdx.x == 0) finish_iteration(a, loss, cnt, dn2, wn2, l1);
+}
+
 static __global__ void __launch_bounds__(1024) k_update_finish(const UpdateArgs a, const double* __restrict__ part, int nparts)
 {
     __shared__ double sm32[32];

@@ -448,10 +448,64 @@ static int reserve_scratch(twtml_ctx* ctx, const twtml_model* m, const twtml_bat
     TW_TRY(ctx->loss_hist.reserve(sizeof(double) * (size_t)std::max(1, m->num_iter)));
     TW_TRY(ctx->out10.reserve(sizeof(double) * 16));
     TW_TRY(ctx->upd_parts.reserve(sizeof(double) * 3 * (size_t)((m->d + kWideCols - 1) / kWideCols)));
+    if (use_sliced(ctx, m, b)) {
+        const size_t slice_len = (size_t)((m->d + ctx->world - 1) / ctx->world);
+        TW_TRY(ctx->slices.reserve(sizeof(double) * (2 * (size_t)ctx->world * slice_len + 2 * (size_t)ctx->world + 8)));
+        TW_TRY(ctx->wprev.reserve(sizeof(double) * (size_t)m->d));
+    }
     return 0;
 }
 
 // block partials -> shard vectors -> (all-gather) ; leaves every rank with all shard vectors
+// wide CSR models on several ranks: all-to-all of gradient slices + sliced update + all-gather of w
+static bool use_sliced(const twtml_ctx* ctx, const twtml_model* m, const twtml_batch* b)
+{
+    return ctx->world > 1 && b->csr && m->d > 2 * kWideCols && getenv("TWTML_NO_SLICED") == nullptr;
+}
+
+static int sliced_update(twtml_ctx* ctx, twtml_model* m, const twtml_batch* b, const UpdateArgs& ua)
+{
+    const int W = ctx->world, d = (int)m->d, slice_len = (d + W - 1) / W;
+    double* mine = ctx->shards.as<double>() + (size_t)ctx->rank * partial_width(b); // [g_0..g_{d-1}, lossSum, count] of this rank
+    double* slices = ctx->slices.as<double>();
+    double* pairs = slices + (size_t)W * slice_len;
+    // slices travel from a staging copy padded to W * slice_len (the tail beyond d carries nothing)
+    double* send = pairs + 2 * W + 2;
+    TW_CUDA(cudaMemcpyAsync(send, mine, sizeof(double) * (size_t)d, cudaMemcpyDeviceToDevice, ctx->stream));
+    TW_NCCL(nccl_api().GroupStart());
+    for (int p = 0; p < W; ++p) {
+        TW_NCCL(nccl_api().Send(send + (size_t)p * slice_len, (size_t)slice_len, ncclDouble, p, ctx->comm, ctx->stream));
+        TW_NCCL(nccl_api().Recv(slices + (size_t)p * slice_len, (size_t)slice_len, ncclDouble, p, ctx->comm, ctx->stream));
+        TW_NCCL(nccl_api().Send(mine + d, 2, ncclDouble, p, ctx->comm, ctx->stream));
+        TW_NCCL(nccl_api().Recv(pairs + 2 * p, 2, ncclDouble, p, ctx->comm, ctx->stream));
+    }
+    TW_NCCL(nccl_api().GroupEnd());
+    TW_CUDA(cudaMemcpyAsync(ctx->wprev.p, m->d_w, sizeof(double) * (size_t)d, cudaMemcpyDeviceToDevice, ctx->stream));
+    SliceArgs sa{};
+    sa.slices = slices;
+    sa.pairs = pairs;
+    sa.w = m->d_w;
+    sa.state = ua.state;
+    sa.W = W;
+    sa.slice_len = slice_len;
+    sa.lo = std::min(d, ctx->rank * slice_len);
+    sa.hi = std::min(d, sa.lo + slice_len);
+    sa.updater = ua.updater;
+    sa.step = ua.step;
+    sa.reg = ua.reg;
+    const int nb = std::max(1, (sa.hi - sa.lo + kWideCols - 1) / kWideCols);
+    k_update_slice<<<nb, 1024, 0, ctx->stream>>>(sa);
+    TW_CUDA(cudaGetLastError());
+    TW_NCCL(nccl_api().AllGather(m->d_w + (size_t)ctx->rank * slice_len, m->d_w, (size_t)slice_len, ncclDouble, ctx->comm, ctx->stream));
+    const int nparts = (d + kWideCols - 1) / kWideCols;
+    k_norms_wide<<<nparts, 1024, 0, ctx->stream>>>(m->d_w, ctx->wprev.as<double>(), d, ua.state, ctx->upd_parts.as<double>());
+    k_slice_finish<<<1, 1024, 0, ctx->stream>>>(ua, pairs, W, ctx->upd_parts.as<double>(), nparts);
+    TW_CUDA(cudaGetLastError());
+    ctx->prof.other_launches += 3;
+    ctx->prof.nccl_calls += 2;
+    return 0;
+}
+
 static bool use_p2p(const twtml_ctx* ctx, const twtml_batch* b)
 {
     return ctx->p2p_ok && !b->csr && partial_width(b) <= kPvCap && b->plan.spr * ctx->world <= kMaxShards;
@@ -605,6 +659,11 @@ static int do_train(twtml_model* m, const twtml_batch* b, bool with_stats, doubl
         ctx->prof.iter_launches += 1;
         TW_TRY(reduce_local(ctx, b, true));
         if (prof && b->csr) TW_CUDA(cudaEventRecord(prof_event(ctx, ne++), ctx->stream));
+        if (use_sliced(ctx, m, b)) {
+            TW_TRY(sliced_update(ctx, m, b, ua));
+            if (i == 1 && with_stats) TW_TRY(reduce_stats(ctx, b));
+            continue;
+        }
         TW_TRY(exchange_shards(ctx, b));
         if (use_p2p(ctx, b)) { // read this iteration's vectors from the local exchange buffer once every writer has signalled
             const int parity = (int)(ctx->xseq & 1ull);
@@ -781,7 +840,7 @@ int32_t twtml_destroy(twtml_ctx* ctx)
     if (ctx->host_done) cudaFreeHost(ctx->host_done);
     if (ctx->comm) nccl_api().CommDestroy(ctx->comm);
     for (DevBuf* b : {&ctx->partials, &ctx->shards, &ctx->stat_partials, &ctx->stat_shards, &ctx->state, &ctx->loss_hist, &ctx->out10,
-                      &ctx->tmp_a, &ctx->tmp_b, &ctx->gather, &ctx->lower, &ctx->upd_parts})
+                      &ctx->tmp_a, &ctx->tmp_b, &ctx->gather, &ctx->lower, &ctx->upd_parts, &ctx->slices, &ctx->wprev})
         b->release();
     for (int i = 0; i < 2; ++i) {
         if (ctx->pin[i]) cudaFreeHost(ctx->pin[i]);
@@ -827,7 +886,8 @@ int32_t twtml_model_create(twtml_ctx* ctx, int64_t num_features, twtml_model** o
     m->ctx = ctx;
     m->d = num_features;
     m->h_w.assign((size_t)num_features, 0.0);
-    cudaError_t e = cudaMalloc(&m->d_w, sizeof(double) * (size_t)(num_features + 2));
+    // room for world equal column slices (the all-gather of a sliced update writes whole slices)
+    cudaError_t e = cudaMalloc(&m->d_w, sizeof(double) * (size_t)(num_features + 2 + ctx->world));
     if (e != cudaSuccess) { delete m; return fail(TWTML_E_OOM, "cudaMalloc weights: %s", cudaGetErrorString(e)); }
     ctx->live_handles += 1;
     *out = m;
