@@ -437,6 +437,8 @@ static int run_pass(twtml_ctx* ctx, const twtml_model* m, const twtml_batch* b, 
 static int partial_width(const twtml_batch* b) { return b->csr ? csr_partial_width(b) : (int)b->ldx + 2; }
 static int loss_slot(const twtml_batch* b) { return b->csr ? (int)b->d : (int)b->ldx; }
 
+static bool use_sliced(const twtml_ctx* ctx, const twtml_model* m, const twtml_batch* b);
+
 static int reserve_scratch(twtml_ctx* ctx, const twtml_model* m, const twtml_batch* b)
 {
     const int pv = partial_width(b);
