@@ -363,7 +363,8 @@ def main():
                              "kernel_ms": kern_ms_per_launch, "bytes_per_launch": int(kbytes),
                              "frac_of_nominal_8TBs": achieved / 8000.0},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
-                "exchange": ("none (1 GPU)" if world == 1 else ("NCCL all-gather, %d calls per step" % nccl_calls if nccl_calls else
+                "exchange": ("none (1 GPU)" if world == 1 else (("NCCL all-to-all of gradient slices + all-gather of w, %d calls per step" if nccl_calls == 2 * iters else
+                                                                  "NCCL all-gather, %d calls per step") % nccl_calls if nccl_calls else
                                                                 "peer-memory stores + flags inside the reduce/update kernels (0 NCCL calls per step)"))}
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"], _, _ = cpu_leg(wl, 3, 1)
