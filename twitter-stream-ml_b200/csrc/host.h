@@ -105,6 +105,10 @@ struct twtml_batch {
     double* win_first_part = nullptr;
     double* win_last_part = nullptr;
     long long nwin = 0;
+    // narrow feature spaces (csr_narrow.cuh): no transpose, only the first row of every warp of a fixed grid
+    bool narrow = false;
+    int nwarps = 0;
+    long long* bounds = nullptr;
     double* diff = nullptr;        // residuals of the current iteration, n
     twtml::Plan plan{};
 };

@@ -442,7 +442,7 @@ static bool use_sliced(const twtml_ctx* ctx, const twtml_model* m, const twtml_b
 static int reserve_scratch(twtml_ctx* ctx, const twtml_model* m, const twtml_batch* b)
 {
     const int pv = partial_width(b);
-    TW_TRY(ctx->partials.reserve(sizeof(double) * (size_t)std::max<long long>(1, b->plan.nblocks) * (b->csr ? 2 : pv)));
+    TW_TRY(ctx->partials.reserve(sizeof(double) * (size_t)std::max<long long>(1, b->plan.nblocks) * (b->csr && !b->narrow ? 2 : pv)));
     TW_TRY(ctx->shards.reserve(sizeof(double) * (size_t)kMaxShards * std::max(1, ctx->world) * pv));
     TW_TRY(ctx->stat_partials.reserve(sizeof(double) * (size_t)std::max<long long>(1, b->plan.nblocks) * kStatStride));
     TW_TRY(ctx->stat_shards.reserve(sizeof(double) * (size_t)kMaxShards * std::max(1, ctx->world) * kStatStride));
@@ -729,7 +729,7 @@ void batch_free_locked(twtml_batch* b)
     cudaStreamSynchronize(b->ctx->stream);
     for (void* p : {(void*)b->X, (void*)b->rowptr, (void*)b->colidx, (void*)b->vals, (void*)b->labels, (void*)b->colptr, (void*)b->rowidx,
                     (void*)b->cvals, (void*)b->headbits, (void*)b->nzcol, (void*)b->win_first_nz, (void*)b->wkey, (void*)b->win_first_part,
-                    (void*)b->win_last_part, (void*)b->diff})
+                    (void*)b->win_last_part, (void*)b->diff, (void*)b->bounds})
         pool_free(b->ctx, p);
     b->ctx->live_handles -= 1;
     delete b;

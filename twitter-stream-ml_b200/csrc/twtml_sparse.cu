@@ -13,6 +13,7 @@
 #include <vector>
 
 #include "csr.cuh"
+#include "csr_narrow.cuh"
 #include "featurize.cuh"
 #include "host.h"
 #include "lower_table.h"
@@ -39,6 +40,30 @@ static int exclusive_sum(twtml_ctx* ctx, const long long* in, long long* out, lo
 
 static unsigned blocks_for(long long n, int threads) { return (unsigned)std::max<long long>(1, (n + threads - 1) / threads); }
 
+// Narrow models: no transpose at all, only the first row of every warp of the single-pass kernel.
+// Returns 1 when the batch does not qualify (the caller then builds the global transpose).
+static int csr_finalize_narrow(twtml_ctx* ctx, twtml_batch* b)
+{
+    const long long n = b->n;
+    const int d = (int)b->d;
+    if (d > kNarrowMaxD || n == 0 || getenv("TWTML_NO_NARROW")) return 1;
+    const int warps = narrow_warps(d);
+    // one partial vector per CTA of a grid fixed here: the plan's "blocks" are those CTAs
+    const long long grid = std::max<long long>(1, std::min<long long>((n + warps - 1) / warps, (long long)ctx->sm_count));
+    const long long G = grid * warps;
+    TW_TRY(dev_alloc(ctx, &b->bounds, (size_t)G + 1));
+    k_narrow_bounds<<<blocks_for(G + 1, 256), 256, 0, ctx->stream>>>(b->rowptr, n, G, b->bounds);
+    TW_CUDA(cudaGetLastError());
+    b->narrow = true;
+    b->nwarps = warps;
+    memset(&b->plan, 0, sizeof(b->plan));
+    b->plan.spr = 1;
+    b->plan.rb = 1;
+    b->plan.nblocks = grid;
+    for (int s2 = 1; s2 <= kMaxShards; ++s2) { b->plan.shard_row0[s2] = n; b->plan.shard_blk0[s2] = grid; }
+    return 0;
+}
+
 // rowptr / colidx / vals / labels are on the device: build the plan, the transpose and the column tasks
 static int csr_finalize(twtml_ctx* ctx, twtml_batch* b)
 {
@@ -48,6 +73,10 @@ static int csr_finalize(twtml_ctx* ctx, twtml_batch* b)
     TW_TRY(ctx_global_rows(ctx, b->n, &b->n_global, &b->row0_global));
     if (b->nnz >= ((long long)1 << 31) || b->n >= ((long long)1 << 31))
         return fail(TWTML_E_INVALID_ARG, "CSR batch too large for 32-bit entry indices (%lld rows, %lld nnz per GPU)", (long long)b->n, (long long)b->nnz);
+    {
+        const int nrc = csr_finalize_narrow(ctx, b);
+        if (nrc <= 0) return nrc; // built (0) or failed (< 0); 1 = not a narrow batch
+    }
     const int d = (int)b->d;
     const long long nnz = b->nnz;
     const long long nwin = (nnz + kWin - 1) / kWin;
@@ -131,9 +160,50 @@ static int new_csr(twtml_ctx* ctx, int64_t n, int64_t d, int64_t nnz, twtml_batc
 // ---- per-iteration launches -----------------------------------------------------------------
 int csr_partial_width(const twtml_batch* b) { return (int)b->d + 2; }
 
+static int launch_narrow(twtml_ctx* ctx, const NarrowArgs& a, int mode, unsigned grid)
+{
+    const size_t smem = narrow_smem_bytes(a.d, a.warps);
+#define TW_NARROW(MODE_)                                                                                  \
+    do {                                                                                                  \
+        auto kern = k_csr_narrow<MODE_>;                                                                  \
+        TW_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));     \
+        kern<<<grid, a.warps * 32, smem, ctx->stream>>>(a);                                               \
+    } while (0)
+    switch (mode) {
+    case MODE_TRAIN: TW_NARROW(MODE_TRAIN); break;
+    case MODE_TRAIN_STATS: TW_NARROW(MODE_TRAIN_STATS); break;
+    case MODE_PREDICT: TW_NARROW(MODE_PREDICT); break;
+    default: TW_NARROW(MODE_PREDICT_STATS); break;
+    }
+#undef TW_NARROW
+    TW_CUDA(cudaGetLastError());
+    return 0;
+}
+
 int csr_launch_iter(twtml_ctx* ctx, const twtml_model* m, const twtml_batch* b, int mode, double* out_pred, double* out_real,
                     int iter_override)
 {
+    if (b->narrow) {
+        NarrowArgs na{};
+        na.rowptr = b->rowptr;
+        na.colidx = b->colidx;
+        na.vals = b->vals;
+        na.labels = b->labels;
+        na.w = m->d_w;
+        na.state = ctx->state.as<TrainState>();
+        na.bounds = b->bounds;
+        na.partials = ctx->partials.as<double>();
+        na.stat_partials = ctx->stat_partials.as<double>();
+        na.out_pred = out_pred;
+        na.out_real = out_real;
+        na.n = b->n;
+        na.d = (int)b->d;
+        na.warps = b->nwarps;
+        na.frac = m->frac;
+        na.row0_global = (unsigned long long)b->row0_global;
+        na.iter_override = iter_override;
+        return launch_narrow(ctx, na, mode, (unsigned)b->plan.nblocks);
+    }
     CsrIterArgs a{};
     a.rowptr = b->rowptr;
     a.colidx = b->colidx;
@@ -174,6 +244,13 @@ int csr_launch_iter(twtml_ctx* ctx, const twtml_model* m, const twtml_batch* b, 
 int csr_reduce(twtml_ctx* ctx, const twtml_batch* b, double* shard_out, const TrainState* gate)
 {
     const int d = (int)b->d;
+    if (b->narrow) { // the fused kernel left one [g, lossSum, count] vector per CTA: add them in CTA order
+        dim3 grid((d + 2 + 31) / 32, 1), block(32, 32);
+        k_shard_reduce<<<grid, block, 0, ctx->stream>>>(ctx->partials.as<double>(), d + 2, b->plan, shard_out, gate);
+        TW_CUDA(cudaGetLastError());
+        ctx->prof.other_launches += 1;
+        return 0;
+    }
     // columns without entries keep gradSum = 0; every other column is written exactly once below
     TW_CUDA(cudaMemsetAsync(shard_out, 0, sizeof(double) * (size_t)d, ctx->stream));
     if (b->nwin > 0) {
