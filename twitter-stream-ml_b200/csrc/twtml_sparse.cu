@@ -40,7 +40,7 @@ static int exclusive_sum(twtml_ctx* ctx, const long long* in, long long* out, lo
 
 static unsigned blocks_for(long long n, int threads) { return (unsigned)std::max<long long>(1, (n + threads - 1) / threads); }
 
-// Narrow models: no transpose at all, only the first row of every warp of the single-pass kernel.
+// Narrow models: no transpose at all, only the first row of every CTA of the single-pass kernel.
 // Returns 1 when the batch does not qualify (the caller then builds the global transpose).
 static int csr_finalize_narrow(twtml_ctx* ctx, twtml_batch* b)
 {
@@ -50,9 +50,8 @@ static int csr_finalize_narrow(twtml_ctx* ctx, twtml_batch* b)
     const int warps = narrow_warps(d);
     // one partial vector per CTA of a grid fixed here: the plan's "blocks" are those CTAs
     const long long grid = std::max<long long>(1, std::min<long long>((n + warps - 1) / warps, (long long)ctx->sm_count));
-    const long long G = grid * warps;
-    TW_TRY(dev_alloc(ctx, &b->bounds, (size_t)G + 1));
-    k_narrow_bounds<<<blocks_for(G + 1, 256), 256, 0, ctx->stream>>>(b->rowptr, n, G, b->bounds);
+    TW_TRY(dev_alloc(ctx, &b->bounds, (size_t)grid + 1));
+    k_narrow_bounds<<<blocks_for(grid + 1, 256), 256, 0, ctx->stream>>>(b->rowptr, n, grid, b->bounds);
     TW_CUDA(cudaGetLastError());
     b->narrow = true;
     b->nwarps = warps;
@@ -148,9 +147,12 @@ static int new_csr(twtml_ctx* ctx, int64_t n, int64_t d, int64_t nnz, twtml_batc
     b->d = d;
     b->nnz = nnz;
     ctx->live_handles += 1; // released by twtml_batch_free, also on the failure paths below and in the callers
+    // colidx / vals end in kNarrowSlack zeroed entries: the narrow kernel reads whole 32-entry slots past a row's end
     int rc = dev_alloc(ctx, &b->rowptr, (size_t)n + 1);
-    if (!rc) rc = dev_alloc(ctx, &b->colidx, (size_t)nnz);
-    if (!rc) rc = dev_alloc(ctx, &b->vals, (size_t)nnz);
+    if (!rc) rc = dev_alloc(ctx, &b->colidx, (size_t)nnz + kNarrowSlack);
+    if (!rc) rc = dev_alloc(ctx, &b->vals, (size_t)nnz + kNarrowSlack);
+    if (!rc && cudaMemsetAsync(b->colidx + nnz, 0, sizeof(int) * kNarrowSlack, ctx->stream) != cudaSuccess) rc = fail(TWTML_E_CUDA, "memset of the CSR slack failed");
+    if (!rc && cudaMemsetAsync(b->vals + nnz, 0, sizeof(double) * kNarrowSlack, ctx->stream) != cudaSuccess) rc = fail(TWTML_E_CUDA, "memset of the CSR slack failed");
     if (!rc) rc = dev_alloc(ctx, &b->labels, (size_t)n);
     if (rc) { batch_free_locked(b); return rc; }
     *out = b;
