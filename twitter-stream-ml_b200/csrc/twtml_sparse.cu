@@ -48,6 +48,7 @@ static int csr_finalize_narrow(twtml_ctx* ctx, twtml_batch* b)
     const int d = (int)b->d;
     if (d > kNarrowMaxD || n == 0 || getenv("TWTML_NO_NARROW")) return 1;
     const int warps = narrow_warps(d);
+    if (warps < 4) return 1;
     // one partial vector per CTA of a grid fixed here: the plan's "blocks" are those CTAs
     const long long grid = std::max<long long>(1, std::min<long long>((n + warps - 1) / warps, (long long)ctx->sm_count));
     TW_TRY(dev_alloc(ctx, &b->bounds, (size_t)grid + 1));
@@ -147,12 +148,10 @@ static int new_csr(twtml_ctx* ctx, int64_t n, int64_t d, int64_t nnz, twtml_batc
     b->d = d;
     b->nnz = nnz;
     ctx->live_handles += 1; // released by twtml_batch_free, also on the failure paths below and in the callers
-    // colidx / vals end in kNarrowSlack zeroed entries: the narrow kernel reads whole 32-entry slots past a row's end
+    // colidx / vals end in kNarrowSlack spare entries: the narrow kernel's bulk copies are 16 bytes wide
     int rc = dev_alloc(ctx, &b->rowptr, (size_t)n + 1);
     if (!rc) rc = dev_alloc(ctx, &b->colidx, (size_t)nnz + kNarrowSlack);
     if (!rc) rc = dev_alloc(ctx, &b->vals, (size_t)nnz + kNarrowSlack);
-    if (!rc && cudaMemsetAsync(b->colidx + nnz, 0, sizeof(int) * kNarrowSlack, ctx->stream) != cudaSuccess) rc = fail(TWTML_E_CUDA, "memset of the CSR slack failed");
-    if (!rc && cudaMemsetAsync(b->vals + nnz, 0, sizeof(double) * kNarrowSlack, ctx->stream) != cudaSuccess) rc = fail(TWTML_E_CUDA, "memset of the CSR slack failed");
     if (!rc) rc = dev_alloc(ctx, &b->labels, (size_t)n);
     if (rc) { batch_free_locked(b); return rc; }
     *out = b;
@@ -169,7 +168,7 @@ static int launch_narrow(twtml_ctx* ctx, const NarrowArgs& a, int mode, unsigned
     do {                                                                                                  \
         auto kern = k_csr_narrow<MODE_>;                                                                  \
         TW_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));     \
-        kern<<<grid, a.warps * 32, smem, ctx->stream>>>(a);                                               \
+        kern<<<grid, (a.warps + 1) * 32, smem, ctx->stream>>>(a);                                               \
     } while (0)
     switch (mode) {
     case MODE_TRAIN: TW_NARROW(MODE_TRAIN); break;
