@@ -338,6 +338,7 @@ def main():
                "includes": "host buffers -> HBM ingest (H2D%s), stats + %d iterations, weights/loss/stats back"
                            % (" + transpose build" if csr else ", pinned, next step's copy overlapping this step's compute", iters)}
 
+    narrow = bool(csr) and d <= 2048 and not os.environ.get("TWTML_NO_NARROW")  # csr_narrow.cuh: kNarrowMaxD
     if rank == 0:
         peak, peak_src = measured_peak()
         achieved = kbytes / (kern_ms_per_launch * 1e-3) / 1e9
@@ -345,8 +346,9 @@ def main():
         try:
             with open(os.path.join(ROOT, "profiles", "iter_kernel_traffic.json")) as f:
                 t = json.load(f)
-                if t.get("rows") == n and t.get("features") == d:
-                    traffic = t["dram_bytes_per_launch"]
+                for ent in (t if isinstance(t, list) else [t]):
+                    if ent.get("rows") == n and ent.get("features") == d and bool(ent.get("csr", False)) == bool(csr):
+                        traffic = ent["dram_bytes_per_launch"]
         except Exception:
             pass
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -354,12 +356,14 @@ def main():
                 "dtype": "f64", "data": "synthetic",
                 "config": {"workload": args.workload, "rows_per_gpu": n, "features": d, "sgd_iterations": iters,
                            "convergence_tol": 0.0, **({"tweets_per_gpu": n_tweets, "nnz_per_gpu": batch.nnz} if tweets is not None else {}), "parallelism": "rows sharded x%d, one exchange of the shard partials per iteration" % world,
-                           "l2": "inputs (%.2f GB/GPU) larger than L2; no flush needed" % ((batch.nnz * 12 * 2 + n * 24) / 1e9 if csr else n * (d + 2) * 8 / 1e9),
+                           "l2": ("inputs (%.3f GB/GPU) about the size of L2, fetched with an evict-first policy: ncu shows every launch reading them from HBM (profiles/); no flush"
+                                  % ((batch.nnz * 12 + n * 16) / 1e9)) if narrow else
+                                 "inputs (%.2f GB/GPU) larger than L2; no flush needed" % ((batch.nnz * 12 * 2 + n * 24) / 1e9 if csr else n * (d + 2) * 8 / 1e9),
                            "timing": "CUDA events on the library stream around each step's iteration loop, max over ranks"},
                 "wall_ms_per_step": wall_ms / args.steps,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": traffic, "peak_source": peak_src,
-                             "kernel": "k_csr_rows + k_csc_windows + k_csc_edges (one read of the CSR credited)" if csr else ("k_dense_iter<1,TRAIN,RL1>" if d + 1 > 992 else "k_dense_iter<1,TRAIN,row lanes>"),
+                             "kernel": ("k_csr_narrow<TRAIN> (single pass over the CSR)" if narrow else "k_csr_rows + k_csc_windows + k_csc_edges (one read of the CSR credited)") if csr else ("k_dense_iter<1,TRAIN,RL1>" if d + 1 > 992 else "k_dense_iter<1,TRAIN,row lanes>"),
                              "kernel_ms": kern_ms_per_launch, "bytes_per_launch": int(kbytes),
                              "frac_of_nominal_8TBs": achieved / 8000.0},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
