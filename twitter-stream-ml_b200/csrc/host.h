@@ -61,6 +61,7 @@ struct twtml_ctx {
     unsigned smem_attr_done = 0; // dense iteration-kernel forms whose dynamic shared-memory limit is raised
     // scratch, reused across calls
     twtml::DevBuf partials, shards, stat_partials, stat_shards, state, loss_hist, out10, tmp_a, tmp_b, gather, lower, upd_parts, slices, wprev;
+    twtml::DevBuf stage[2]; // flat landing zone of pinned dense ingest: [0] compute stream, [1] copy stream
     // pinned staging ring for host -> device ingest
     void* pin[2] = {nullptr, nullptr};
     size_t pin_bytes = 0;
