@@ -55,6 +55,23 @@ def main():
             ms.trainOnBatch(bs)
             ws_ref, hs_ref = oracle_c.sgd(la, 504, np.zeros(504), csr=(rp, ci, va), step_size=0.005, num_iterations=6, convergence_tol=0.0)
             assert np.max(np.abs(ms.latestModel().weights.toArray() - ws_ref)) / np.max(np.abs(ws_ref)) < 1e-6
+            wsn = ms.latestModel().weights.toArray()
+            wtn = torch.from_numpy(wsn).cuda(); w0n = wtn.clone(); dist.broadcast(w0n, src=0)
+            assert torch.equal(wtn, w0n), "ranks disagree on the narrow CSR weights"
+            # the same model when only rank 0 has rows (an interval with fewer tweets than GPUs): the other ranks feed empty
+            # batches and still take part in every exchange
+            k = 3
+            me = (tw.StreamingLinearRegressionWithSGD(ctx=ctx).setNumIterations(4).setStepSize(0.005)
+                  .setConvergenceTol(0.0).setInitialWeights(tw.Vectors.zeros(504)))
+            if rank == 0:
+                be = ctx.batch_from_csr(k, 504, rp[:k + 1], ci[:rp[k]], va[:rp[k]], la[:k])
+            else:
+                be = ctx.batch_from_csr(0, 504, np.zeros(1, np.int64), np.zeros(0, np.int32), np.zeros(0), np.zeros(0))
+            ste, _, _ = me.step(be)
+            we_ref, _ = oracle_c.sgd(la[:k], 504, np.zeros(504), csr=(rp[:k + 1], ci[:rp[k]], va[:rp[k]]), step_size=0.005,
+                                     num_iterations=4, convergence_tol=0.0)
+            assert ste["batch"] == k
+            assert np.max(np.abs(me.latestModel().weights.toArray() - we_ref)) / np.max(np.abs(we_ref)) < 1e-6
             # a wide hashed model takes the sliced exchange (all-to-all of gradient slices, sliced update, all-gather of w)
             dw = 20000 + 4
             rp, ci, va, la = oracle_c.synth_csr(n, 20000, seed=10)

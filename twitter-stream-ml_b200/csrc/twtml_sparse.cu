@@ -46,7 +46,7 @@ static int csr_finalize_narrow(twtml_ctx* ctx, twtml_batch* b)
 {
     const long long n = b->n;
     const int d = (int)b->d;
-    if (d > kNarrowMaxD || n == 0 || getenv("TWTML_NO_NARROW")) return 1;
+    if (d > kNarrowMaxD || getenv("TWTML_NO_NARROW")) return 1; // a function of the model width only: every rank decides alike
     const int warps = narrow_warps(d);
     if (warps < 4) return 1;
     // one partial vector per CTA of a grid fixed here: the plan's "blocks" are those CTAs
