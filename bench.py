@@ -194,7 +194,7 @@ def main():
     ap.add_argument("--workload", default="dense_1m", choices=sorted(WORKLOADS))
     ap.add_argument("--rows", type=int, default=0, help="override rows per GPU (testing)")
     ap.add_argument("--iters", type=int, default=0, help="override SGD iterations per micro-batch (testing)")
-    ap.add_argument("--e2e-steps", type=int, default=4)
+    ap.add_argument("--e2e-steps", type=int, default=8)
     ap.add_argument("--e2e-sync", action="store_true", help="blocking ingest in the e2e leg (A/B against the pipelined default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

@@ -62,6 +62,8 @@ struct twtml_ctx {
     // scratch, reused across calls
     twtml::DevBuf partials, shards, stat_partials, stat_shards, state, loss_hist, out10, tmp_a, tmp_b, gather, lower, upd_parts, slices, wprev;
     twtml::DevBuf stage[2]; // flat landing zone of pinned dense ingest: [0] compute stream, [1] copy stream
+    cudaStream_t spread_stream = nullptr;      // k_repitch runs here, beside the next chunk's copy
+    cudaEvent_t stage_ev[2][2][2] = {};        // [landing zone][half][0: chunk copied, 1: chunk spread]
     // pinned staging ring for host -> device ingest
     void* pin[2] = {nullptr, nullptr};
     size_t pin_bytes = 0;

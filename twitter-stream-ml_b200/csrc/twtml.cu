@@ -380,7 +380,9 @@ __global__ void k_repitch(const double* __restrict__ flat, double* __restrict__ 
 
 // Page-locked, densely packed host rows -> the batch's pitched rows.  A pitched (2-D) copy of 8 KB rows reaches ~45 GB/s
 // on this link, a flat one ~55 GB/s: so the rows land flat in a small device buffer (two halves, alternating) and a kernel
-// spreads each chunk to the row pitch and drops the labels in.  Everything is ordered on `stream`.
+// spreads each chunk to the row pitch and drops the labels in.  The copies are ordered on `stream`; the kernels run on the
+// context's spread stream, beside the next chunk's copy (events per half: copied -> spread -> may be overwritten); `stream`
+// ends up waiting for the last kernel, so whatever the caller orders after this call on `stream` sees the whole batch.
 static const size_t kStageChunkBytes = (size_t)64 << 20;
 static cudaError_t flat_dense_ingest(twtml_ctx* ctx, int which, cudaStream_t stream, twtml_batch* b, const double* X, const double* labels_dev)
 {
@@ -389,17 +391,31 @@ static cudaError_t flat_dense_ingest(twtml_ctx* ctx, int which, cudaStream_t str
     const size_t half = sizeof(double) * (size_t)rows_per * (size_t)d;
     const size_t need = n <= rows_per ? sizeof(double) * (size_t)n * (size_t)d : 2 * half; // a small batch uses one half only
     if (ctx->stage[which].reserve(need)) return cudaErrorMemoryAllocation;
+    cudaStream_t spread = ctx->spread_stream;
+    cudaError_t e;
+    // the labels (copied on `stream` before this call) and, for a zone used before, its last kernels: order the spread stream
+    // behind `stream` once; every kernel below additionally waits for its own chunk's copy
+    if ((e = cudaEventRecord(ctx->stage_ev[which][0][0], stream)) != cudaSuccess) return e;
+    if ((e = cudaStreamWaitEvent(spread, ctx->stage_ev[which][0][0], 0)) != cudaSuccess) return e;
     int k = 0;
-    for (int64_t r0 = 0; r0 < n; r0 += rows_per, k ^= 1) {
+    int64_t chunk = 0;
+    for (int64_t r0 = 0; r0 < n; r0 += rows_per, k ^= 1, ++chunk) {
         const int64_t nr = std::min(rows_per, n - r0);
         double* st = reinterpret_cast<double*>(static_cast<char*>(ctx->stage[which].p) + (size_t)k * half);
-        cudaError_t e = cudaMemcpyAsync(st, X + r0 * d, sizeof(double) * (size_t)nr * (size_t)d, cudaMemcpyHostToDevice, stream);
-        if (e != cudaSuccess) return e;
+        // this half was last read by the kernel of chunk - 2
+        if (chunk >= 2 && (e = cudaStreamWaitEvent(stream, ctx->stage_ev[which][k][1], 0)) != cudaSuccess) return e;
+        if ((e = cudaMemcpyAsync(st, X + r0 * d, sizeof(double) * (size_t)nr * (size_t)d, cudaMemcpyHostToDevice, stream)) != cudaSuccess) return e;
+        if ((e = cudaEventRecord(ctx->stage_ev[which][k][0], stream)) != cudaSuccess) return e;
+        if ((e = cudaStreamWaitEvent(spread, ctx->stage_ev[which][k][0], 0)) != cudaSuccess) return e;
         const long long total = nr * b->ldx;
         const unsigned grid = (unsigned)std::min<long long>((total + 255) / 256, (long long)ctx->sm_count * 16);
-        k_repitch<<<grid, 256, 0, stream>>>(st, b->X + r0 * b->ldx, b->ldx, (int)d, labels_dev + r0, nr);
+        k_repitch<<<grid, 256, 0, spread>>>(st, b->X + r0 * b->ldx, b->ldx, (int)d, labels_dev + r0, nr);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
+        if ((e = cudaEventRecord(ctx->stage_ev[which][k][1], spread)) != cudaSuccess) return e;
     }
+    // both halves' last kernels before anything later on `stream` (the next batch's copies into this zone included)
+    for (int h = 0; h < 2; ++h)
+        if (chunk > h && (e = cudaStreamWaitEvent(stream, ctx->stage_ev[which][h][1], 0)) != cudaSuccess) return e;
     return cudaSuccess;
 }
 
@@ -816,6 +832,10 @@ static int32_t create_common(int32_t device, int32_t rank, int32_t world, const 
     cudaError_t se = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
     if (se != cudaSuccess) { delete c; return fail(TWTML_E_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(se)); }
     cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
+    cudaStreamCreateWithFlags(&c->spread_stream, cudaStreamNonBlocking);
+    for (auto& zone : c->stage_ev)
+        for (auto& half : zone)
+            for (auto& ev : half) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
     {
         cudaMemPoolProps props{};
         props.allocType = cudaMemAllocationTypePinned;
@@ -889,6 +909,11 @@ int32_t twtml_destroy(twtml_ctx* ctx)
     if (ctx->pool) cudaMemPoolDestroy(ctx->pool);
     cudaStreamDestroy(ctx->stream);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+    if (ctx->spread_stream) cudaStreamDestroy(ctx->spread_stream);
+    for (auto& zone : ctx->stage_ev)
+        for (auto& half : zone)
+            for (auto& ev : half)
+                if (ev) cudaEventDestroy(ev);
     delete ctx;
     return 0;
 }
