@@ -287,18 +287,19 @@ def main():
     # ---- end to end through the C ABI with HOST buffers: ingest (H2D) + stats + train + results (D2H)
     e2e = None
     if (args.workload != "dense_16m" or args.rows) and args.e2e_steps > 0:
+        def pin(a):  # page-locked copy of a host array (the library then DMAs straight from it)
+            raw = torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).pin_memory().numpy()
+            return raw.view(a.dtype)
+
         if tweets is not None:
             h2d = sum(getattr(tweets, k).nbytes for k in ("text_utf16", "text_off", "retweet_count", "followers", "favourites",
                                                            "friends", "created_ms", "is_retweet"))
-            def pin(a):  # page-locked copy of a host column (the library then DMAs straight from it)
-                raw = torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).pin_memory().numpy()
-                return raw.view(a.dtype)
             ptweets = tw.TweetBatch.from_arrays(*(pin(getattr(tweets, k)) for k in
                                                  ("text_utf16", "text_off", "retweet_count", "followers", "favourites", "friends",
                                                   "created_ms", "is_retweet")))
             make = lambda: ctx.batch_from_tweets(ptweets, now_ms, 100, 1000, wl["buckets"])
         elif csr:
-            host = batch.export_csr()                                  # host copy of this rank's rows
+            host = tuple(pin(a) for a in batch.export_csr())           # page-locked host copy of this rank's rows
             h2d = sum(a.nbytes for a in host)
             make = lambda: ctx.batch_from_csr(n, d, *host)
         else:
