@@ -31,7 +31,7 @@
 namespace twtml {
 
 constexpr int kNarrowMaxD = 2048;
-constexpr int kNarrowMaxWarps = 16;                   // consumer warps (one more warp produces: 512 threads, 128 registers each)
+constexpr int kNarrowMaxWarps = 16;                   // consumer warps (one more warp produces: 544 threads)
 constexpr int kNarrowThreadsMax = (kNarrowMaxWarps + 1) * 32;
 constexpr int kNarrowK = 3;                           // entries per lane kept in registers between the two halves
 constexpr int kNarrowTileLog = 10;
