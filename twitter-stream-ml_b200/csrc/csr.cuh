@@ -23,6 +23,7 @@
 namespace twtml {
 
 constexpr int kCsrThreads = 256; // LPR lanes per row (4 / 8 / 16 by average row length), kCsrThreads / LPR rows at a time
+constexpr int kCsrUnroll = 4;                // entries per lane and row whose loads and gathers are in flight together
 constexpr int kWin = 256;                   // CSC entries per window (8 head-mask words)
 
 struct CsrIterArgs {
@@ -78,28 +79,29 @@ __global__ void __launch_bounds__(kCsrThreads) k_csr_rows(const CsrIterArgs a)
                 k[h] = valids[h] ? a.rowptr[row] + l8 : 0;
                 e[h] = valids[h] ? a.rowptr[row + 1] : 0;
             }
+            constexpr int U = kCsrUnroll; // entries per lane and row in flight
             while (k[0] < e[0] || k[1] < e[1]) {
-                int ci[2][2];
-                double vv[2][2];
+                int ci[2][U];
+                double vv[2][U];
 #pragma unroll
                 for (int h = 0; h < 2; ++h)
 #pragma unroll
-                    for (int u = 0; u < 2; ++u) {
+                    for (int u = 0; u < U; ++u) {
                         const long long kk = k[h] + LPR * u;
                         const bool p = kk < e[h];
                         ci[h][u] = p ? a.colidx[kk] : 0;
                         vv[h][u] = p ? a.vals[kk] : 0.0;
                     }
-                double ww[2][2];
+                double ww[2][U];
 #pragma unroll
                 for (int h = 0; h < 2; ++h)
 #pragma unroll
-                    for (int u = 0; u < 2; ++u) ww[h][u] = a.w[ci[h][u]];
+                    for (int u = 0; u < U; ++u) ww[h][u] = a.w[ci[h][u]];
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
-                    accs[h] = fma(vv[h][0], ww[h][0], accs[h]); // entries k, k+LPR, k+2 LPR, ... in this order per lane
-                    accs[h] = fma(vv[h][1], ww[h][1], accs[h]);
-                    k[h] += 2 * LPR;
+#pragma unroll
+                    for (int u = 0; u < U; ++u) accs[h] = fma(vv[h][u], ww[h][u], accs[h]); // entries k, k+LPR, k+2 LPR, ... in this order per lane
+                    k[h] += U * LPR;
                 }
             }
           }
