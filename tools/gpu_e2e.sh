@@ -1,4 +1,5 @@
 #!/bin/bash
+# Dense ingest: host-to-device rates (tools/pcie_probe.py), the dense parity tests, the default bench line (e2e leg).
 mkdir -p gpurun_out
 python tools/pcie_probe.py 2>&1 | tail -8
 timeout -k 10 900 python -m pytest tests/test_dense_gpu.py tests/test_fuzz_gpu.py tests/test_cpp_facade.py -m gpu -x -q 2>&1 | tail -3
