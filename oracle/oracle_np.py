@@ -168,7 +168,7 @@ def sgd(y, d, w0, X=None, csr=None, step_size=0.1, num_iterations=50, mini_batch
             g = Xs.T @ diff
             hist.append(float((diff * diff).sum() / 2.0) / cnt + reg_val)
             w_new, reg_val = _update(updater, w, g / cnt, step_size, i, reg_param)
-            if i >= 2:
+            if len(hist) >= 2:        # previousWeights != None [U]: an earlier iteration also drew a non-empty sample
                 converged = np.linalg.norm(w - w_new) < convergence_tol * max(np.linalg.norm(w_new), 1.0)
             w = w_new
         i += 1

@@ -343,7 +343,8 @@ static void tree_combine(agg_t* a, int P, int64_t d)
  *                loss += diff*diff/2; count += 1
  *      if m > 0: lossHistory += lossSum/m + regVal
  *                (w, regVal) = updater.compute(w, gradSum/m, stepSize, i, reg)
- *                converged = i >= 2 && ||w_prev - w|| < tol * max(||w||, 1)
+ *                converged = (an earlier iteration also had m > 0: previousWeights != None)
+ *                            && ||w_prev - w|| < tol * max(||w||, 1)
  *   The iteration counter restarts at 1 on every micro-batch.
  *
  * Rows come either dense (X, ldx) or CSR (rowptr/colidx/vals) -- exactly one non-NULL.
@@ -408,11 +409,12 @@ static int32_t sgd_core(
         tree_combine(agg, P, d);
         int64_t m = agg[0].cnt;
         if (m > 0) {
+            const int had_previous = nhist >= 1; /* previousWeights != None: set by an earlier iteration with m > 0 */
             loss_history[nhist++] = agg[0].loss / (double)m + reg_val;
             memcpy(wprev, w, sizeof(double) * (size_t)d);
             for (int64_t j = 0; j < d; ++j) gavg[j] = agg[0].g[j] / (double)m;
             reg_val = updater_compute(updater_kind, w, gavg, d, step_size, i, reg_param);
-            if (i >= 2) {
+            if (had_previous) {
                 double dn = 0.0, wn = 0.0;
                 for (int64_t j = 0; j < d; ++j) {
                     double df = wprev[j] - w[j];

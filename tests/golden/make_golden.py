@@ -82,6 +82,42 @@ exp_rows = [
 dump("featurizer_kat.json", dict(now_ms=NOW, rt_begin=100, rt_end=1000, num_text_features=1000,
                                  hash_kats=hash_kats, tweets=tweets, expected_rows=exp_rows))
 
+# 1b. Edge cases of the text half, each its own call (own HashingTF width F):
+#     a lone high surrogate followed by a letter is just two UTF-16 units (String.sliding works on chars, not code
+#     points); a lone low surrogate alone is a one-unit text; the empty text has no term at all; F = 1 sends every
+#     term to bucket 0; F = 7 is a small prime width.
+edge_groups = [
+    dict(num_text_features=1000, tweets=[
+        tweet([0xD83D, 0x61], 100, 1, 1, 1, 1),      # 31*55357 + 97 = 1716164 -> 164
+        tweet([0xDE00], 100, 2, 2, 2, 2),            # one unit: hashCode = 56832 -> 832
+        tweet([], 1000, 3, 3, 3, 3),                 # L = 0: numeric slots only
+        tweet([0x61, 0xD83D, 0xDE00, 0xDC00], 500, 4, 4, 4, 4),   # a, a surrogate pair, then a stray low surrogate
+    ], expected_rows=[
+        dict(idx=[164, 1000, 1001, 1002, 1003], val=[1.0, 1e-12, 1e-12, 1e-12, 1e-14], label=100.0),
+        dict(idx=[832, 1000, 1001, 1002, 1003], val=[1.0, 2e-12, 2e-12, 2e-12, 2 * 1e-14], label=100.0),
+        dict(idx=[1000, 1001, 1002, 1003], val=[3e-12, 3e-12, 3e-12, 3 * 1e-14], label=1000.0),
+        # 31*97+55357 = 58364 -> 364 ; 31*55357+56832 = 1772899 -> 899 ; 31*56832+56320 = 1818112 -> 112
+        dict(idx=[112, 364, 899, 1000, 1001, 1002, 1003], val=[1.0, 1.0, 1.0, 4e-12, 4e-12, 4e-12, 4 * 1e-14], label=500.0),
+    ]),
+    dict(num_text_features=1, tweets=[
+        tweet([0x61, 0x62, 0x63], 200, 0, 0, 0, 0),  # "abc": both bigrams in bucket 0
+        tweet([0x7A], 300, 0, 0, 0, 0),              # "z": its single one-unit term in bucket 0
+        tweet([], 400, 0, 0, 0, 0),
+    ], expected_rows=[
+        dict(idx=[0, 1, 2, 3, 4], val=[2.0, 0.0, 0.0, 0.0, 0.0], label=200.0),
+        dict(idx=[0, 1, 2, 3, 4], val=[1.0, 0.0, 0.0, 0.0, 0.0], label=300.0),
+        dict(idx=[1, 2, 3, 4], val=[0.0, 0.0, 0.0, 0.0], label=400.0),
+    ]),
+    dict(num_text_features=7, tweets=[
+        tweet([0x61, 0x62, 0x63], 200, 7, 0, 0, 0),  # ab = 3105 = 7*443 + 4 ; bc = 3137 = 7*448 + 1
+    ], expected_rows=[
+        dict(idx=[1, 4, 7, 8, 9, 10], val=[1.0, 1.0, 7e-12, 0.0, 0.0, 0.0], label=200.0),
+    ]),
+]
+assert (31 * 0xD83D + 0x61) % 1000 == 164 and 0xDE00 % 1000 == 832
+assert [(31 * a + b) % 1000 for a, b in zip([0x61, 0xD83D, 0xDE00], [0xD83D, 0xDE00, 0xDC00])] == [364, 899, 112]
+dump("featurizer_edge_kat.json", dict(now_ms=NOW, rt_begin=100, rt_end=1000, groups=edge_groups))
+
 # ------------------------------------------------------------------------------------------
 # 2. Utils.round (Utils.scala:4-5): decimal HALF_UP, ties away from zero.
 # ------------------------------------------------------------------------------------------

@@ -68,6 +68,20 @@ def test_featurizer_kat(oracle):
         assert labels[r] == e["label"]
 
 
+def test_featurizer_edge_kats(oracle):
+    """Lone surrogates, empty and one-unit texts, F = 1 and F = 7 (tests/golden/featurizer_edge_kat.json)."""
+    g = golden("featurizer_edge_kat.json")
+    for grp in g["groups"]:
+        F = grp["num_text_features"]
+        rowptr, colidx, vals, labels = oracle.featurize(*_pack(grp["tweets"]), g["now_ms"], g["rt_begin"], g["rt_end"], F)
+        assert len(labels) == len(grp["expected_rows"])
+        for r, e in enumerate(grp["expected_rows"]):
+            sl = slice(rowptr[r], rowptr[r + 1])
+            assert colidx[sl].tolist() == e["idx"] and vals[sl].tolist() == e["val"] and labels[r] == e["label"]
+        py = onp.featurize([dict(t, text=_units_to_str(t["units"])) for t in grp["tweets"]], g["now_ms"], g["rt_begin"], g["rt_end"], F)
+        assert py[1].tolist() == colidx.tolist() and py[2].tolist() == vals.tolist()
+
+
 def _units_to_str(units):
     return np.array(units, np.uint16).tobytes().decode("utf-16-le", "surrogatepass")
 
@@ -154,6 +168,31 @@ def test_sgd_default_tolerance_stops_early(oracle):
     assert len(h) == 2
     wn, hn = onp.sgd(y, 16, np.zeros(16), X=X, step_size=1e-5, num_iterations=50)
     assert len(hn) == 2 and rel(w, wn) < 1e-12
+
+
+def first_sample_empty_case(onp_mod):
+    """miniBatchFraction under which the one-row batch at global row 0 draws NO row at iteration 1 but its row at
+    iterations 2 and 3 (the counter-based sampler gives u = 0.844, 0.610, 0.019 there)."""
+    frac = 0.7
+    assert [bool(onp_mod.sample_mask(i, 0, 1, frac)[0]) for i in (1, 2, 3)] == [False, True, True]
+    return frac
+
+
+def test_convergence_check_waits_for_a_previous_nonempty_iteration(oracle):
+    """GradientDescent [U] tests convergence only when previousWeights != None, i.e. from the SECOND iteration that drew
+    a non-empty sample -- not from i = 2.  With an empty first sample and a step so small that any two consecutive
+    weight vectors are within tolerance, the loop must run iterations 2 and 3 (two loss entries) and stop there; gating on
+    i >= 2 would stop after iteration 2 with one entry."""
+    frac = first_sample_empty_case(onp)
+    X, y = np.array([[1.0, 1.0]]), np.array([1.0])
+    kw = dict(step_size=1e-4, num_iterations=50, mini_batch_fraction=frac, convergence_tol=0.001, row0=0)
+    w, h = oracle.sgd(y, 2, np.zeros(2), X=X, **kw)
+    wn, hn = onp.sgd(y, 2, np.zeros(2), X=X, **kw)
+    assert len(h) == 2 and len(hn) == 2
+    assert rel(w, wn) < 1e-13 and rel(h, hn) < 1e-13
+    # by hand: iteration 2 moves w by eta_2 * (0 - 1) * (1, 1) = 1e-4/sqrt(2) per coordinate, iteration 3 by 1e-4/sqrt(3) * (1 - 2 w)
+    e2 = 1e-4 / math.sqrt(2)
+    assert abs(w[0] - (e2 + 1e-4 / math.sqrt(3) * (1 - 2 * e2))) < 1e-18 and h[0] == 0.5
 
 
 def test_sampler_is_partition_invariant(oracle):

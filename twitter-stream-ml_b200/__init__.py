@@ -6,7 +6,7 @@ importable by that name; `import twtml_b200` (the alias package at the repo root
 from . import _lib
 from ._lib import TwtmlError, build
 from .api import (Batch, Context, DenseVector, DStream, LabeledPoint, LinearRegressionModel, MllibHelper,
-                  SparseVector, StreamingLinearRegressionWithSGD, TweetBatch, Vectors, stats_payload)
+                  SparseVector, StreamingLinearRegressionWithSGD, TweetBatch, Vectors, lightning_series, stats_payload)
 
 __all__ = ["Batch", "Context", "DenseVector", "DStream", "LabeledPoint", "LinearRegressionModel", "MllibHelper",
-           "SparseVector", "StreamingLinearRegressionWithSGD", "TweetBatch", "TwtmlError", "Vectors", "build", "stats_payload", "_lib"]
+           "SparseVector", "StreamingLinearRegressionWithSGD", "TweetBatch", "TwtmlError", "Vectors", "build", "lightning_series", "stats_payload", "_lib"]

@@ -463,6 +463,16 @@ def stats_payload(count, stats):
                        "realStddev": int(stats["real_stdev"]), "predStddev": int(stats["pred_stdev"])}, separators=(",", ":"))
 
 
+def lightning_series(stats, real, pred):
+    """The four series SessionStats.update appends to the Lightning line-streaming plot for one batch
+    (SessionStats.scala:26-33): Array(real, pred, Array.fill(batch)(realStdev), Array.fill(batch)(predStdev)) --
+    the labels, the Utils.round-ed predictions, and the two already rounded standard deviations repeated once
+    per row (batch.toInt of them).  `stats`, `real`, `pred` are what predictStats / step return."""
+    n = int(stats["batch"])
+    return [np.asarray(real, np.float64), np.asarray(pred, np.float64),
+            np.full(n, float(stats["real_stdev"])), np.full(n, float(stats["pred_stdev"]))]
+
+
 def _is_empty(rdd):
     return rdd.isEmpty() if isinstance(rdd, Batch) else len(rdd) == 0
 

@@ -55,7 +55,6 @@ struct twtml_ctx {
     double* xbuf = nullptr;                 // this rank's exchange buffer
     double* peer[twtml::kMaxShards] = {};   // every rank's buffer as mapped here (peer[rank] == xbuf)
     bool peer_ipc[twtml::kMaxShards] = {};  // mapped with cudaIpcOpenMemHandle (to be closed)
-    unsigned long long xseq = 0;            // exchange sequence number, the same on every rank
     int* host_done = nullptr;     // mapped pinned word: the update kernel sets it when a training loop has ended
     int* host_done_dev = nullptr; // ... its device alias
     unsigned smem_attr_done = 0; // dense iteration-kernel forms whose dynamic shared-memory limit is raised

@@ -52,20 +52,26 @@ static __global__ void __launch_bounds__(1024) k_shard_reduce(const double* __re
 // between processes, direct peer access between threads of one process).  In iteration number seq a
 // rank's k_shard_reduce_p2p stores its shard vectors straight into EVERY rank's buffer (parity seq & 1)
 // and, once its last CTA is done, stores seq into its flag slot on every rank; the update kernel of a
-// rank spins on its own flag slots until all writers have reached seq.  Two parities suffice: nobody
-// can start iteration seq + 2 before every rank has finished reading iteration seq.
+// rank spins on its own flag slots until all writers have reached seq.
+// The sequence number lives ON THE DEVICE (one word of the local buffer, advanced by the update kernel
+// after it has read the vectors): it counts the exchanges that really ran, not the launches the host
+// enqueued -- after an early convergence the remaining launches of a call are no-ops and leave it alone.
+// Every rank takes the same decisions from the same bits, so the words stay equal across ranks.  Two
+// parities then suffice: a rank starts exchange seq + 2 only after its update kernel saw every flag at
+// seq + 1, i.e. after every peer's update kernel of exchange seq has finished reading parity seq & 1.
 constexpr int kPvCap = 4104;
 constexpr size_t kXbufDataDoubles = (size_t)2 * kMaxShards * kPvCap;
 constexpr size_t kXbufBytes = kXbufDataDoubles * 8 + 2 * kMaxShards * 8 + 64;
 
 struct PeerExchange {
     double* peer[kMaxShards]; // base of rank r's exchange buffer, as mapped here
-    unsigned* counter;        // local CTA counter
     int world, rank;
-    unsigned long long seq;
 };
 
 __host__ __device__ __forceinline__ unsigned long long* xbuf_flags(double* base) { return reinterpret_cast<unsigned long long*>(base + kXbufDataDoubles); }
+// local words behind the flags: the CTA counter of k_shard_reduce_p2p and the number of the last exchange this rank completed
+__host__ __device__ __forceinline__ unsigned* xbuf_counter(double* base) { return reinterpret_cast<unsigned*>(xbuf_flags(base) + 2 * kMaxShards); }
+__host__ __device__ __forceinline__ unsigned long long* xbuf_seq(double* base) { return xbuf_flags(base) + 2 * kMaxShards + 1; }
 
 static __global__ void __launch_bounds__(1024) k_shard_reduce_p2p(const double* __restrict__ partials, int pv, Plan plan, PeerExchange px,
                                                            const TrainState* state)
@@ -91,7 +97,9 @@ static __global__ void __launch_bounds__(1024) k_shard_reduce_p2p(const double* 
     }
     sm[threadIdx.y][threadIdx.x] = acc;
     __syncthreads();
-    const int parity = (int)(px.seq & 1ull);
+    double* mine = px.peer[px.rank];
+    const unsigned long long seq = *xbuf_seq(mine) + 1ull; // advanced only by the update kernel that follows on this stream
+    const int parity = (int)(seq & 1ull);
     if (threadIdx.y == 0 && col < pv) {
         double tot = 0.0;
 #pragma unroll
@@ -103,11 +111,12 @@ static __global__ void __launch_bounds__(1024) k_shard_reduce_p2p(const double* 
     __syncthreads();
     if (threadIdx.x == 0 && threadIdx.y == 0) {
         const unsigned total = gridDim.x * gridDim.y;
-        if (atomicAdd(px.counter, 1u) == total - 1u) { // last CTA of this rank: everything above is globally visible
-            *px.counter = 0u;
+        unsigned* counter = xbuf_counter(mine);
+        if (atomicAdd(counter, 1u) == total - 1u) { // last CTA of this rank: everything above is globally visible
+            *counter = 0u;
             __threadfence_system();
             for (int r = 0; r < px.world; ++r)
-                *reinterpret_cast<volatile unsigned long long*>(xbuf_flags(px.peer[r]) + parity * kMaxShards + px.rank) = px.seq;
+                *reinterpret_cast<volatile unsigned long long*>(xbuf_flags(px.peer[r]) + parity * kMaxShards + px.rank) = seq;
         }
     }
 }
@@ -135,30 +144,38 @@ struct UpdateArgs {
     int nshards, pv, d, ldx;
     int max_iter, updater;
     double step, reg, tol;
-    // peer exchange: wait until wait_n writers have stored wait_seq into wait_flags[0..wait_n)
-    const unsigned long long* wait_flags;
-    unsigned long long wait_seq;
+    // peer exchange (xbuf != null): the vectors of exchange seq = *xbuf_seq + 1 are read from this rank's exchange buffer
+    // once its wait_n writers have stored seq into their flag slots; `shards` is then ignored
+    double* xbuf;
     int wait_n;
     int* host_done; // mapped host word set when the loop is over, so a single-GPU host can stop enqueuing no-op iterations
 };
 
 constexpr int kPeerTimeoutMark = 0x7E57; // TrainState::pad after a peer never showed up
 
-// returns false when a peer did not arrive within ~10 s (the kernel then stops the training loop)
-__device__ __forceinline__ bool wait_for_peers(const UpdateArgs& a)
+// Peer exchange: points a.shards at this exchange's vectors and waits for every writer.  Returns false when a peer did
+// not arrive within ~10 s (the kernel then stops the training loop).  The writers are other GPUs: the flags are read
+// with system-scope volatile loads, every thread fences at system scope before it touches the vectors, and the
+// vectors themselves are read past L1 (__ldcg in update_column / shard_totals).
+__device__ __forceinline__ bool wait_for_peers(UpdateArgs& a, unsigned long long& seq)
 {
     __shared__ int timed_out;
-    if (!a.wait_flags) return true;
+    seq = 0ull;
+    if (!a.xbuf) return true;
+    seq = *xbuf_seq(a.xbuf) + 1ull;
+    const int parity = (int)(seq & 1ull);
+    a.shards = a.xbuf + (size_t)parity * kMaxShards * kPvCap;
     if (threadIdx.x == 0) timed_out = 0;
     __syncthreads();
     if (threadIdx.x < a.wait_n) {
-        const volatile unsigned long long* f = a.wait_flags + threadIdx.x;
+        const volatile unsigned long long* f = xbuf_flags(a.xbuf) + parity * kMaxShards + threadIdx.x;
         const long long t0 = clock64();
-        while (*f < a.wait_seq)
+        while (*f < seq)
             if (clock64() - t0 > 20000000000ll) { timed_out = 1; break; }
+        __threadfence_system();
     }
     __syncthreads();
-    __threadfence();
+    __threadfence_system();
     if (timed_out) {
         if (threadIdx.x == 0) { a.state->done = 1; a.state->pad = kPeerTimeoutMark; }
         return false;
@@ -185,7 +202,7 @@ __device__ __forceinline__ void update_column(const UpdateArgs& a, int j, double
                                               double& l1)
 {
     double g = 0.0;
-    for (int s = 0; s < a.nshards; ++s) g += a.shards[(long long)s * a.pv + j];
+    for (int s = 0; s < a.nshards; ++s) g += __ldcg(a.shards + (long long)s * a.pv + j);
     g = g / cnt;
     const double wo = a.w[j];
     double wn;
@@ -212,8 +229,8 @@ __device__ __forceinline__ void shard_totals(const UpdateArgs& a, double& loss, 
 {
     loss = cnt = 0.0;
     for (int s = 0; s < a.nshards; ++s) {
-        loss += a.shards[(long long)s * a.pv + a.ldx];
-        cnt += a.shards[(long long)s * a.pv + a.ldx + 1];
+        loss += __ldcg(a.shards + (long long)s * a.pv + a.ldx);
+        cnt += __ldcg(a.shards + (long long)s * a.pv + a.ldx + 1);
     }
 }
 
@@ -224,11 +241,12 @@ __device__ __forceinline__ void finish_iteration(const UpdateArgs& a, double los
     const int i = st->iter;
     bool converged = false;
     if (cnt > 0.0) {
+        const bool had_previous = st->nhist >= 1; // previousWeights != None [U]: an earlier iteration of this batch had m > 0
         a.loss_hist[st->nhist] = loss / cnt + st->reg_val;
         st->nhist += 1;
         const double wn = sqrt(wn2);
         st->reg_val = a.updater == 1 ? 0.5 * a.reg * wn * wn : (a.updater == 2 ? l1 * a.reg : 0.0);
-        if (i >= 2) converged = sqrt(dn2) < a.tol * fmax(wn, 1.0);
+        if (had_previous) converged = sqrt(dn2) < a.tol * fmax(wn, 1.0);
     }
     st->last_count = cnt;
     st->iter = i + 1;
@@ -239,11 +257,13 @@ __device__ __forceinline__ void finish_iteration(const UpdateArgs& a, double los
 }
 
 // Narrow models (the dense path): one CTA of 1024 threads does the whole update.
-static __global__ void __launch_bounds__(1024) k_update(const UpdateArgs a)
+static __global__ void __launch_bounds__(1024) k_update(const UpdateArgs a_in)
 {
     __shared__ double sm32[32];
+    UpdateArgs a = a_in;
     if (a.state->done) return;
-    if (!wait_for_peers(a)) return;
+    unsigned long long seq;
+    if (!wait_for_peers(a, seq)) return;
     double cnt, loss;
     shard_totals(a, loss, cnt);
     double dn2 = 0.0, wn2 = 0.0, l1 = 0.0;
@@ -253,8 +273,11 @@ static __global__ void __launch_bounds__(1024) k_update(const UpdateArgs a)
     }
     dn2 = block_sum_1024(dn2, sm32);
     wn2 = block_sum_1024(wn2, sm32);
-    l1 = block_sum_1024(l1, sm32);
-    if (threadIdx.x == 0) finish_iteration(a, loss, cnt, dn2, wn2, l1);
+    l1 = block_sum_1024(l1, sm32); // (its barriers: every thread has read the vectors by now)
+    if (threadIdx.x == 0) {
+        finish_iteration(a, loss, cnt, dn2, wn2, l1);
+        if (a.xbuf) *xbuf_seq(a.xbuf) = seq; // this exchange is complete on this rank
+    }
 }
 
 // Wide models (hashed text, d ~ 2^20): the columns are spread over many CTAs, each leaving its three

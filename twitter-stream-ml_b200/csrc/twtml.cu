@@ -582,10 +582,8 @@ static int reduce_local(twtml_ctx* ctx, const twtml_batch* b, bool gated)
     } else if (gated && use_p2p(ctx, b)) {
         PeerExchange px{};
         for (int r = 0; r < ctx->world; ++r) px.peer[r] = ctx->peer[r];
-        px.counter = reinterpret_cast<unsigned*>(xbuf_flags(ctx->xbuf) + 2 * kMaxShards);
         px.world = ctx->world;
         px.rank = ctx->rank;
-        px.seq = ++ctx->xseq;
         dim3 grid((pv + 31) / 32, spr), block(32, 32);
         k_shard_reduce_p2p<<<grid, block, 0, ctx->stream>>>(ctx->partials.as<double>(), pv, b->plan, px, gate);
         TW_CUDA(cudaGetLastError());
@@ -721,10 +719,7 @@ static int do_train(twtml_model* m, const twtml_batch* b, bool with_stats, doubl
         }
         TW_TRY(exchange_shards(ctx, b));
         if (use_p2p(ctx, b)) { // read this iteration's vectors from the local exchange buffer once every writer has signalled
-            const int parity = (int)(ctx->xseq & 1ull);
-            ua.shards = ctx->xbuf + (size_t)parity * kMaxShards * kPvCap;
-            ua.wait_flags = xbuf_flags(ctx->xbuf) + parity * kMaxShards;
-            ua.wait_seq = ctx->xseq;
+            ua.xbuf = ctx->xbuf;
             ua.wait_n = ctx->world;
         }
         if (m->d <= 2 * kWideCols) {

@@ -46,6 +46,7 @@ static __device__ __align__(256) double g_static_scratch[kScratchDoubles];
 constexpr int kMaxDevices = 64;
 static std::mutex g_setup_mu;
 static double* g_scratch_addr[kMaxDevices] = {nullptr};
+static unsigned g_smem_attr_done[kMaxDevices] = {0}; // per device: kernel forms whose shared-memory limit is already raised
 
 // once per device, with that device current
 static int setup_device(int device, double** out)
@@ -66,7 +67,14 @@ template <int CP, bool RL1>
 static int launch_stats_pass(twtml_ctx* ctx, const DenseCfg& c, const DenseIterArgs& a)
 {
     auto kern = k_dense_iter<CP, MODE_PREDICT_STATS, RL1>;
-    TW_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    constexpr unsigned form = 1u << (CP == 1 ? (RL1 ? 1 : 0) : (CP == 2 ? 2 : 3));
+    {   // once per device and kernel form (set-up work, like the address look-up)
+        std::lock_guard<std::mutex> lk(g_setup_mu);
+        if (!(g_smem_attr_done[ctx->device] & form)) {
+            TW_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+            g_smem_attr_done[ctx->device] |= form;
+        }
+    }
     long long grid = std::min<long long>((long long)ctx->sm_count * c.grid_per_sm, a.plan.nblocks);
     kern<<<(unsigned)grid, kIterThreads, c.smem, ctx->stream>>>(a);
     TW_CUDA(cudaGetLastError());

@@ -294,13 +294,17 @@ int32_t twtml_batch_from_csr(twtml_ctx* ctx, int64_t n, int64_t d, const int64_t
     if (n < 0 || d < 1 || d > ((int64_t)1 << 30) || !rowptr || (n > 0 && !labels)) return fail(TWTML_E_INVALID_ARG, "twtml_batch_from_csr: bad shape or null data");
     const int64_t nnz = rowptr[n] - rowptr[0];
     if (rowptr[0] != 0 || nnz < 0 || (nnz > 0 && (!colidx || !vals))) return fail(TWTML_E_INVALID_ARG, "twtml_batch_from_csr: rowptr must start at 0 and be non-decreasing");
+    // the row pointers alone first (a malformed one must be refused before any index is read through it)
+    for (int64_t r = 0; r < n; ++r)
+        if (rowptr[r] < 0 || rowptr[r] > rowptr[r + 1] || rowptr[r + 1] > nnz)
+            return fail(TWTML_E_INVALID_ARG, "row %lld: rowptr must be non-decreasing within [0, rowptr[n]]", (long long)r);
     { // Vectors.sparse require()s strictly increasing, in-range indices [U]; checked on all host threads
         std::atomic<int64_t> bad_row(-1);
         const unsigned hw = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
         const int nt = (int)std::min<int64_t>(hw, std::max<int64_t>(1, n / 4096));
         auto scan = [&](int64_t lo, int64_t hi) {
             for (int64_t r = lo; r < hi && bad_row.load(std::memory_order_relaxed) < 0; ++r) {
-                bool ok = rowptr[r + 1] >= rowptr[r];
+                bool ok = true;
                 for (int64_t k = rowptr[r]; ok && k < rowptr[r + 1]; ++k)
                     ok = colidx[k] >= 0 && colidx[k] < d && (k == rowptr[r] || colidx[k] > colidx[k - 1]);
                 if (!ok) bad_row.store(r);
@@ -313,7 +317,7 @@ int32_t twtml_batch_from_csr(twtml_ctx* ctx, int64_t n, int64_t d, const int64_t
             for (auto& t : th) t.join();
         }
         if (bad_row.load() >= 0)
-            return fail(TWTML_E_INVALID_ARG, "row %lld: rowptr must not decrease and indices must be strictly increasing and < %lld", (long long)bad_row.load(), (long long)d);
+            return fail(TWTML_E_INVALID_ARG, "row %lld: indices must be strictly increasing and < %lld", (long long)bad_row.load(), (long long)d);
     }
     Guard g(ctx);
     twtml_batch* b = nullptr;
