@@ -2,21 +2,25 @@
 """bench.py -- SGD row*iterations/s of the per-micro-batch learning path on N B200s.
 
 A "step" is one micro-batch: the hot path (numIterations fused SGD-iteration passes + their
-fixed-order reduce/update) over a synthetic dense micro-batch already resident in HBM.
+fixed-order reduce/update) over a synthetic micro-batch already resident in HBM.
 
   python bench.py --gpus N --steps K --warmup W            (N > 1: launched under torchrun)
   python bench.py --impl reference ...                      (the CPU restatement, all host cores)
 
 Workloads (BASELINE.json configs):
-  dense_1m    2^20 rows/GPU x 1004 features, 20 iterations  (configs[1]; the default)
-  dense_16m   2^24 rows/GPU x 1004 features, 50 iterations  (configs[2], HBM-roofline config; no e2e:
-              134.75 GB does not stage through host memory)
-  dense_d128  2^24 rows/GPU x 128 features, 50 iterations (the narrow-row shape of configs[3])
+  dense_16m   2^24 rows/GPU x 1004 features, 50 iterations  (configs[2], the HBM-roofline config the metric is quoted
+              on: THE DEFAULT).  Its end-to-end leg streams the 135 GB batch from one 2^20-row page-locked host buffer,
+              re-sent 16 times per step through twtml_batch_dense_begin / _append (every byte crosses the host link
+              inside the timed region; the host never holds more than 8.4 GB).
+  dense_1m    2^20 rows/GPU x 1004 features, 20 iterations  (configs[1])
+  dense_d128  2^24 rows/GPU x 128 features, 50 iterations   (the narrow-row shape of configs[3])
   tweets_1m   10^6 synthetic tweets/GPU (SURVEY 8d config 1 recipe) -> device featuriser (HashingTF(1000) + 4) ->
-              CSR of the rows that pass the retweet filter (~14 %), 50 iterations, reference step size 0.005
+              CSR of the rows that pass the retweet filter (~14 %), 50 iterations, reference step size 0.005  (configs[0])
   csr_2m      2^21 rows/GPU, 2^20+4 columns, ~24 nnz/row CSR, 50 iterations (configs[4] per GPU)
+The JSON line is the default workload's; at N = 1 it also carries "sub_records" with the same measurements
+(value, roofline, e2e) for dense_1m, tweets_1m and csr_2m (--sub none turns them off).
 Multi-GPU: every rank holds the same number of rows (weak scaling); per iteration the ranks exchange
-their (gradSum, lossSum, count) shard vectors with one NCCL all-gather.
+their (gradSum, lossSum, count) shard vectors (peer-memory stores, NCCL as the fallback).
 """
 import argparse
 import json
@@ -41,8 +45,11 @@ WORKLOADS["tweets_1m"] = dict(rows=1000000, d=1004, iters=50, step=0.005, csr=Tr
 # configs[4], distribution A: the same tweets hashed into 2^20 buckets -- char bigrams of mostly-ASCII text land in a few
 # thousand of them, i.e. extreme column skew
 WORKLOADS["tweets_1m_wide"] = dict(rows=1000000, d=(1 << 20) + 4, iters=50, step=0.005, csr=True, tweets=True, buckets=1 << 20)
+DEFAULT_WORKLOAD = "dense_16m"
+DEFAULT_SUBS = "dense_1m,tweets_1m,csr_2m"
 METRIC = "sgd_row_iterations_per_s"
 UNIT = "row*iter/s"
+CHUNK_ROWS = 1 << 20          # rows of the page-locked host buffer the dense e2e legs stream from
 
 
 def measured_peak():
@@ -53,6 +60,13 @@ def measured_peak():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def workload_config(name, wl, world):
+    """What both arms (ours and --impl reference) run: the same keys and values on both lines."""
+    return {"workload": name, "rows_per_gpu": wl["rows"], "features": wl["d"], "sgd_iterations": wl["iters"],
+            "step_size": wl["step"], "convergence_tol": 0.0, "mini_batch_fraction": 1.0,
+            "layout": "csr" if wl.get("csr") else "dense", "parallelism": "rows sharded x%d" % world}
+
+
 def synth_tweets(n, seed):
     """Vectorised form of the SURVEY.md 8d config-1 recipe: lower-case text of U[2,140] tokens over letters, digits,
     punctuation, 16 Latin-1 accented letters and 8 emoji (two UTF-16 units each); retweet ~ Bernoulli(0.7); log-uniform
@@ -60,7 +74,7 @@ def synth_tweets(n, seed):
     import numpy as np
     rng = np.random.default_rng(seed)
     now = 1464739200000
-    one = [ord(c) for c in "abcdefghijklmnopqrstuvwxyz0123456789 #@.,!?:/" + "\u00e0\u00e1\u00e2\u00e3\u00e4\u00e5\u00e7\u00e8\u00e9\u00ea\u00eb\u00ec\u00ed\u00f1\u00f6\u00fc"]
+    one = [ord(c) for c in "abcdefghijklmnopqrstuvwxyz0123456789 #@.,!?:/" + "àáâãäåçèéêëìíñöü"]
     emoji = [0x1F600, 0x1F601, 0x1F602, 0x1F923, 0x1F60D, 0x1F44D, 0x1F525, 0x1F389]
     first = np.array(one + [0xD800 + ((c - 0x10000) >> 10) for c in emoji], np.uint16)
     second = np.array([0] * len(one) + [0xDC00 + ((c - 0x10000) & 0x3FF) for c in emoji], np.uint16)
@@ -115,14 +129,48 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-def cpu_leg(wl, steps, warmup, budget_s=15.0, threads=None):
+def host_cores():
+    """Cores this process may run on -- NOT OMP_NUM_THREADS, which torchrun sets to 1 for its workers."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
+def bind_to_gpu_numa_node(local):
+    """Run this process on the CPUs of the NUMA node the GPU hangs off, so that the page-locked host buffers it
+    allocates next are local to the GPU's PCIe root (first-touch placement).  Returns a description, or None."""
+    try:
+        out = subprocess.run(["nvidia-smi", "-i", str(local), "--query-gpu=pci.bus_id", "--format=csv,noheader"],
+                             capture_output=True, text=True, timeout=20).stdout.strip().lower()
+        bdf = out[-12:] if len(out) >= 12 else out          # 00000000:1b:00.0 -> 0000:1b:00.0
+        with open("/sys/bus/pci/devices/%s/numa_node" % bdf) as f:
+            node = int(f.read().strip())
+        if node < 0:
+            return {"node": node, "bound": False}
+        with open("/sys/devices/system/node/node%d/cpulist" % node) as f:
+            cpus = set()
+            for part in f.read().strip().split(","):
+                lo, _, hi = part.partition("-")
+                cpus.update(range(int(lo), int(hi or lo) + 1))
+        allowed = cpus & os.sched_getaffinity(0)
+        if not allowed:
+            return {"node": node, "bound": False}
+        os.sched_setaffinity(0, allowed)
+        return {"node": node, "bound": True, "cpus": len(allowed)}
+    except Exception as e:                                     # no sysfs / no nvidia-smi: leave the process where it is
+        return {"bound": False, "why": str(e)[:80]}
+
+
+def cpu_leg(wl, steps, warmup, threads=None, max_seconds=150.0):
     """The CPU restatement (oracle/twtml_oracle.c, OpenMP over row partitions like Spark local[N]) on a
     bounded sample of the workload: same width, same iteration count, fewer rows (dense: 2^17 rows;
-    CSR: 2^18 rows; tweets: 10^5 tweets, featurised by the restatement inside the timed step)."""
+    CSR: 2^18 rows; tweets: 10^5 tweets, featurised by the restatement inside the timed step).  Runs `steps` timed
+    steps after `warmup` untimed ones unless that would take longer than max_seconds (then fewer, and says so)."""
     from oracle import oracle_c
     import numpy as np
     oracle_c.build()
-    cores = threads or oracle_c.max_threads()
+    cores = threads or host_cores()
     d, iters = wl["d"], wl["iters"]
     w0 = np.zeros(d)
     common = dict(step_size=wl["step"], num_iterations=iters, convergence_tol=0.0, partitions=cores, threads=cores)
@@ -147,7 +195,7 @@ def cpu_leg(wl, steps, warmup, budget_s=15.0, threads=None):
         what = "%d of %d rows x %d columns CSR, %d iterations" % (rows, wl["rows"], d, iters)
     else:
         rows = 1 << 17
-        X, y = oracle_c.synth_dense(rows, d, seed=42)
+        X, y = oracle_c.synth_dense(rows, d, seed=42, threads=cores)
 
         def step():
             oracle_c.sgd(y, d, w0, X=X, **common)
@@ -156,8 +204,8 @@ def cpu_leg(wl, steps, warmup, budget_s=15.0, threads=None):
     t0 = time.perf_counter()
     step()                                              # also the first warm-up step
     once = time.perf_counter() - t0
-    k = max(1, min(steps, int(budget_s / max(once, 1e-3))))
-    for _ in range(min(max(0, warmup - 1), 2)):
+    k = max(1, min(steps, int(max_seconds / max(once, 1e-3)) - warmup))
+    for _ in range(max(0, warmup - 1)):
         step()
     t0 = time.perf_counter()
     for _ in range(k):
@@ -168,34 +216,273 @@ def cpu_leg(wl, steps, warmup, budget_s=15.0, threads=None):
     return dict(value=value, unit=UNIT, cores=cores, kind="port", sample=sample), dt / k * 1e3, k
 
 
-def run_reference(args, wl):
+def run_reference(args, name, wl):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     cb, ms, k = cpu_leg(wl, args.steps, args.warmup)
-    cb2, _, _ = cpu_leg(wl, 2, 1, budget_s=8.0, threads=2)            # README.md:55 of the reference: --master local[2]
+    cb2, _, _ = cpu_leg(wl, 2, 1, threads=2, max_seconds=20.0)            # README.md:55 of the reference: --master local[2]
     line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": k,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f64", "data": "synthetic",
-            "config": {"workload": args.workload, "rows_per_gpu": wl["rows"], "features": wl["d"], "sgd_iterations": wl["iters"],
-                       "note": "CPU restatement of the reference's MLlib 1.6.1 path (the Scala/Spark reference cannot run here: no JVM)"},
+            "dtype": "f64", "data": "synthetic", "config": workload_config(name, wl, args.gpus),
+            "note": "CPU restatement of the reference's MLlib 1.6.1 path (the Scala/Spark reference cannot run here: no JVM), "
+                    "timed on a bounded row sample of the workload (cpu_baseline.sample)",
             "cpu_baseline": cb, "cpu_baseline_local2": cb2,
             "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
 
 
+def traffic_entry(n, d, csr):
+    """DRAM bytes per launch of the iteration kernel from the committed ncu capture of this kernel at this shape
+    (profiles/iter_kernel_traffic.json); None when no capture of this shape exists."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "iter_kernel_traffic.json")) as f:
+            t = json.load(f)
+        for ent in (t if isinstance(t, list) else [t]):
+            if ent.get("rows") == n and ent.get("features") == d and bool(ent.get("csr", False)) == bool(csr):
+                return ent["dram_bytes_per_launch"], ent.get("source")
+    except Exception:
+        pass
+    return None, None
+
+
+class Bench:
+    """One process's (one rank's) measurement state."""
+
+    def __init__(self, args):
+        import torch
+        import torch.distributed as dist
+
+        import twtml_b200 as tw
+        self.torch, self.dist, self.tw, self.args = torch, dist, tw, args
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if self.world != args.gpus:
+            raise SystemExit("--gpus %d but WORLD_SIZE=%d: launch N > 1 with torch.distributed.run" % (args.gpus, self.world))
+        self.numa = None if args.no_numa_bind else bind_to_gpu_numa_node(self.local)
+        torch.cuda.set_device(self.local)
+        nccl_id = None
+        if self.world > 1:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
+            ids = [tw.Context.nccl_unique_id() if self.rank == 0 else None]
+            dist.broadcast_object_list(ids, src=0)
+            nccl_id = ids[0]
+        self.ctx = tw.Context(self.local, self.rank, self.world, nccl_id)
+        self.ctx.profile(True)
+        self.chunk = None          # page-locked (X, y) of CHUNK_ROWS x 1004, shared by the dense e2e legs
+
+    def barrier(self):
+        self.torch.cuda.synchronize()
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def max_over_ranks(self, v):
+        if self.world == 1:
+            return v
+        t = self.torch.tensor([v], dtype=self.torch.float64, device="cuda")
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def pin(self, a):
+        """Page-locked copy of a host array (the library then DMAs straight from it)."""
+        import numpy as np
+        raw = self.torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).pin_memory().numpy()
+        return raw.view(a.dtype).reshape(a.shape)
+
+    def host_chunk(self, d, rows):
+        """>= rows x d page-locked rows + labels: generated on the device, copied out once, then page-locked."""
+        if self.chunk is None or self.chunk[0].shape[1] != d or self.chunk[0].shape[0] < rows:
+            self.chunk = None
+            g = self.ctx.batch_synth_dense(rows, d, seed=42, row0=self.rank * rows)
+            Xh, yh = g.export_dense()
+            g.free()
+            Xp = self.torch.from_numpy(Xh).pin_memory().numpy()
+            del Xh
+            self.chunk = (Xp, self.torch.from_numpy(yh).pin_memory().numpy())
+        return self.chunk
+
+    # ------------------------------------------------------------------------------------------------
+    def run(self, name, wl, steps, warmup, e2e_steps, sample_clocks):
+        import numpy as np
+        tw, ctx, world, rank = self.tw, self.ctx, self.world, self.rank
+        n, d, iters = wl["rows"], wl["d"], wl["iters"]
+        model = (tw.StreamingLinearRegressionWithSGD(ctx=ctx).setNumIterations(iters).setStepSize(wl["step"])
+                 .setMiniBatchFraction(1.0).setConvergenceTol(0.0).setInitialWeights(tw.Vectors.zeros(d)))
+        csr = bool(wl.get("csr"))
+        tweets = n_tweets = None
+        if wl.get("tweets"):
+            cols, now_ms = synth_tweets(n, 20160601 + rank)
+            tweets = tw.TweetBatch.from_arrays(**cols)
+            batch = ctx.batch_from_tweets(tweets, now_ms, 100, 1000, wl["buckets"])   # filter + featurise on the GPU
+            n_tweets, n = n, batch.n                                     # the metric counts the rows that train
+        elif csr:
+            batch = ctx.batch_synth_csr(n, wl["d_text"], seed=42, row0=rank * n)
+        else:
+            batch = ctx.batch_synth_dense(n, d, seed=42, row0=rank * n)  # resident in HBM before the timed region
+        nnz = batch.nnz
+
+        for _ in range(warmup):
+            model.trainOnBatch(batch)
+        sampler = ClockSampler(self.local) if (sample_clocks and rank == 0) else None
+        if sampler:
+            sampler.start()
+        dev_ms = kern_ms = 0.0
+        launches = kern_launches = 0
+        self.barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            model.trainOnBatch(batch)
+            p = ctx.last_profile()
+            dev_ms += p.loop_ms
+            kern_ms += p.iter_kernel_ms
+            kern_launches += p.iter_launches
+            launches += p.iter_launches + p.other_launches
+            nccl_calls = p.nccl_calls
+            kbytes = p.iter_kernel_bytes
+        self.barrier()
+        wall_ms = (time.perf_counter() - t0) * 1e3
+        clocks = sampler.stop() if sampler else None
+        dev_ms = self.max_over_ranks(dev_ms)
+        wall_ms = self.max_over_ranks(wall_ms)
+        kern_ms_per_launch = self.max_over_ranks(kern_ms / max(kern_launches, 1))
+        assert len(model.lastLossHistory) == iters, "iterations were skipped"
+        value = world * n * iters * steps / (dev_ms * 1e-3)
+
+        # ---- end to end through the C ABI with HOST buffers: ingest (H2D) + stats + train + results (D2H)
+        e2e = None
+        if e2e_steps > 0:
+            streamed = False
+            if tweets is not None:
+                names = ("text_utf16", "text_off", "retweet_count", "followers", "favourites", "friends", "created_ms", "is_retweet")
+                h2d = sum(getattr(tweets, k).nbytes for k in names)
+                ptweets = tw.TweetBatch.from_arrays(*(self.pin(getattr(tweets, k)) for k in names))
+                make = lambda: ctx.batch_from_tweets(ptweets, now_ms, 100, 1000, wl["buckets"], wait=self.args.e2e_sync)
+                how = "page-locked tweet columns -> device featuriser"
+            elif csr:
+                host = tuple(self.pin(a) for a in batch.export_csr())           # page-locked host copy of this rank's rows
+                h2d = sum(a.nbytes for a in host)
+                make = lambda: ctx.batch_from_csr(n, d, *host, wait=self.args.e2e_sync)
+                how = "page-locked CSR arrays" + ("" if d <= 2048 else " + transpose build")
+            else:
+                batch.free()                                                    # two 135 GB batches do not fit
+                batch = None
+                Xp, yp = self.host_chunk(d, min(n, CHUNK_ROWS))
+                h2d = n * (d + 1) * 8
+                if n <= CHUNK_ROWS:
+                    Xv, yv = Xp[:n], yp[:n]
+                    make = (lambda: ctx.batch_from_dense(Xv, yv)) if self.args.e2e_sync else (lambda: ctx.batch_from_dense_async(Xv, yv))
+                    how = "page-locked rows, flat 64 MB copies + k_repitch"
+                else:
+                    streamed = True
+
+                    def make():
+                        b = ctx.batch_dense_begin(n, d)
+                        for r0 in range(0, n, CHUNK_ROWS):
+                            nr = min(CHUNK_ROWS, n - r0)
+                            b.append(Xp[:nr], yp[:nr])
+                        return b
+                    how = ("one %d-row page-locked buffer re-sent %d times per step through twtml_batch_dense_begin/_append"
+                           % (CHUNK_ROWS, (n + CHUNK_ROWS - 1) // CHUNK_ROWS))
+            model.setInitialWeights(tw.Vectors.zeros(d))
+            t_ingest = t_step = 0.0
+
+            def run(k):
+                nonlocal t_ingest, t_step
+                nxt = make()
+                for i in range(k):
+                    b = nxt
+                    t0 = time.perf_counter()
+                    # every step's rows cross the host link inside the timed region; where HBM holds two batches the next
+                    # step's ingest is issued before this step computes and overlaps it
+                    nxt = make() if (i + 1 < k and not streamed) else None
+                    t1 = time.perf_counter()
+                    st, _, _ = model.step(b, want_arrays=False)
+                    w = model.latestModel().weights.toArray()
+                    t_ingest += t1 - t0
+                    t_step += time.perf_counter() - t1
+                    b.free()
+                    if streamed and i + 1 < k:
+                        t2 = time.perf_counter()
+                        nxt = make()
+                        t_ingest += time.perf_counter() - t2
+                return st, w
+
+            run(1)
+            t_ingest = t_step = 0.0
+            self.barrier()
+            t0 = time.perf_counter()
+            st, w = run(e2e_steps)
+            self.barrier()
+            e2e_s = self.max_over_ranks(time.perf_counter() - t0)
+            assert st["batch"] >= n and np.all(np.isfinite(w))
+            e2e = {"value": world * n * iters * e2e_steps / e2e_s, "unit": UNIT,
+                   "h2d_bytes_per_step": int(world * h2d),
+                   "d2h_bytes_per_step": int(world * (d * 8 + iters * 8 + 80)),
+                   "steps": e2e_steps, "ingest_ms_per_step": t_ingest / e2e_steps * 1e3,
+                   "compute_ms_per_step": t_step / e2e_steps * 1e3,
+                   "h2d_GBps_effective_per_gpu": h2d * e2e_steps / e2e_s / 1e9,
+                   "overlap": "none: HBM holds one batch of this size, ingest and compute alternate" if streamed else
+                              ("none (--e2e-sync)" if self.args.e2e_sync else "step t+1's ingest runs beside step t's compute"),
+                   "numa": self.numa,
+                   "includes": "host buffers -> HBM ingest (%s), stats + %d iterations, weights/loss/stats back" % (how, iters)}
+
+        narrow = csr and d <= 2048 and not os.environ.get("TWTML_NO_NARROW")  # csr_narrow.cuh: kNarrowMaxD
+        rec = None
+        if rank == 0:
+            peak, peak_src = measured_peak()
+            achieved = kbytes / (kern_ms_per_launch * 1e-3) / 1e9
+            traffic, traffic_src = traffic_entry(n, d, csr) if world == 1 else (None, None)
+            resident_gb = (nnz * 12 * (1 if narrow else 2) + n * 24) / 1e9 if csr else n * (d + 2) * 8 / 1e9
+            cfg = workload_config(name, dict(wl, rows=wl["rows"]), world)
+            rec = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warmup,
+                   "ms_per_step": dev_ms / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                   "dtype": "f64", "data": "synthetic", "config": cfg,
+                   "notes": {"rows_trained_per_gpu": n,
+                             **({"tweets_per_gpu": n_tweets, "nnz_per_gpu": nnz} if tweets is not None else {}),
+                             "exchange": "one exchange of the shard partials per iteration",
+                             "l2": ("inputs (%.3f GB/GPU) about the size of L2, fetched with an evict-first policy: ncu shows every launch "
+                                    "reading them from HBM (profiles/); no flush" % resident_gb) if narrow else
+                                   "inputs (%.2f GB/GPU) larger than L2; no flush needed" % resident_gb,
+                             "timing": "CUDA events on the library stream around each step's iteration loop, max over ranks"},
+                   "wall_ms_per_step": wall_ms / steps,
+                   "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                                "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
+                                "kernel": ("k_csr_narrow<TRAIN> (single pass over the CSR)" if narrow else "k_csr_rows + k_csc_windows + k_csc_edges (one read of the CSR credited)") if csr else ("k_dense_iter<1,TRAIN,RL1>" if d + 1 > 992 else "k_dense_iter<1,TRAIN,row lanes>"),
+                                "kernel_ms": kern_ms_per_launch, "bytes_per_launch": int(kbytes),
+                                "frac_of_nominal_8TBs": achieved / 8000.0},
+                   "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
+                   "exchange": ("none (1 GPU)" if world == 1 else (("NCCL all-to-all of gradient slices + all-gather of w, %d calls per step" if nccl_calls == 2 * iters else
+                                                                     "NCCL all-gather, %d calls per step") % nccl_calls if nccl_calls else
+                                                                   "peer-memory stores + flags inside the reduce/update kernels (0 NCCL calls per step)"))}
+        if batch is not None:
+            batch.free()
+        model.free()
+        return rec
+
+    def close(self):
+        self.chunk = None
+        self.ctx.close()
+        if self.world > 1:
+            self.dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="dense_1m", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--sub", default=None, help="comma-separated workloads measured as sub_records (default at N = 1 with the "
+                                                 "default workload: %s; 'none' turns them off)" % DEFAULT_SUBS)
     ap.add_argument("--rows", type=int, default=0, help="override rows per GPU (testing)")
     ap.add_argument("--iters", type=int, default=0, help="override SGD iterations per micro-batch (testing)")
-    ap.add_argument("--e2e-steps", type=int, default=8)
+    ap.add_argument("--e2e-steps", type=int, default=-1, help="timed end-to-end steps (default: 2 for streamed 135 GB batches, else 8)")
     ap.add_argument("--e2e-sync", action="store_true", help="blocking ingest in the e2e leg (A/B against the pipelined default)")
+    ap.add_argument("--no-numa-bind", action="store_true", help="do not move the process to the GPU's NUMA node before allocating host buffers")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     wl = dict(WORKLOADS[args.workload])
@@ -204,186 +491,30 @@ def main():
     if args.iters:
         wl["iters"] = args.iters
     if args.impl == "reference":
-        return run_reference(args, wl)
+        return run_reference(args, args.workload, wl)
     if args.warmup < 3:
         args.warmup = 3
+    full_affinity = os.sched_getaffinity(0)
 
-    import numpy as np
-    import torch
-    import torch.distributed as dist
-
-    import twtml_b200 as tw
-
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if world != args.gpus:
-        raise SystemExit("--gpus %d but WORLD_SIZE=%d: launch N > 1 with torch.distributed.run" % (args.gpus, world))
-    torch.cuda.set_device(local)
-    nccl_id = None
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-        ids = [tw.Context.nccl_unique_id() if rank == 0 else None]
-        dist.broadcast_object_list(ids, src=0)
-        nccl_id = ids[0]
-
-    def barrier():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def max_over_ranks(v):
-        if world == 1:
-            return v
-        t = torch.tensor([v], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    n, d, iters = wl["rows"], wl["d"], wl["iters"]
-    ctx = tw.Context(local, rank, world, nccl_id)
-    ctx.profile(True)
-    model = (tw.StreamingLinearRegressionWithSGD(ctx=ctx).setNumIterations(iters).setStepSize(wl["step"])
-             .setMiniBatchFraction(1.0).setConvergenceTol(0.0).setInitialWeights(tw.Vectors.zeros(d)))
-    csr = bool(wl.get("csr"))
-    tweets = None
-    if wl.get("tweets"):
-        cols, now_ms = synth_tweets(n, 20160601 + rank)
-        tweets = tw.TweetBatch.from_arrays(**cols)
-        batch = ctx.batch_from_tweets(tweets, now_ms, 100, 1000, wl["buckets"])   # filter + featurise on the GPU
-        n_tweets, n = n, batch.n                                     # the metric counts the rows that train
-    elif csr:
-        batch = ctx.batch_synth_csr(n, wl["d_text"], seed=42, row0=rank * n)
-    else:
-        batch = ctx.batch_synth_dense(n, d, seed=42, row0=rank * n)  # resident in HBM before the timed region
-
-    for _ in range(args.warmup):
-        model.trainOnBatch(batch)
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-    dev_ms = kern_ms = 0.0
-    launches = kern_launches = 0
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        model.trainOnBatch(batch)
-        p = ctx.last_profile()
-        dev_ms += p.loop_ms
-        kern_ms += p.iter_kernel_ms
-        kern_launches += p.iter_launches
-        launches += p.iter_launches + p.other_launches
-        nccl_calls = p.nccl_calls
-        kbytes = p.iter_kernel_bytes
-    barrier()
-    wall_ms = (time.perf_counter() - t0) * 1e3
-    clocks = sampler.stop() if rank == 0 else None
-    dev_ms = max_over_ranks(dev_ms)
-    wall_ms = max_over_ranks(wall_ms)
-    kern_ms_per_launch = max_over_ranks(kern_ms / max(kern_launches, 1))
-    assert len(model.lastLossHistory) == iters, "iterations were skipped"
-    value = world * n * iters * args.steps / (dev_ms * 1e-3)
-
-    # ---- end to end through the C ABI with HOST buffers: ingest (H2D) + stats + train + results (D2H)
-    e2e = None
-    if (args.workload != "dense_16m" or args.rows) and args.e2e_steps > 0:
-        def pin(a):  # page-locked copy of a host array (the library then DMAs straight from it)
-            raw = torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).pin_memory().numpy()
-            return raw.view(a.dtype)
-
-        if tweets is not None:
-            h2d = sum(getattr(tweets, k).nbytes for k in ("text_utf16", "text_off", "retweet_count", "followers", "favourites",
-                                                           "friends", "created_ms", "is_retweet"))
-            ptweets = tw.TweetBatch.from_arrays(*(pin(getattr(tweets, k)) for k in
-                                                 ("text_utf16", "text_off", "retweet_count", "followers", "favourites", "friends",
-                                                  "created_ms", "is_retweet")))
-            make = lambda: ctx.batch_from_tweets(ptweets, now_ms, 100, 1000, wl["buckets"])
-        elif csr:
-            host = tuple(pin(a) for a in batch.export_csr())           # page-locked host copy of this rank's rows
-            h2d = sum(a.nbytes for a in host)
-            make = lambda: ctx.batch_from_csr(n, d, *host)
-        else:
-            Xh, yh = batch.export_dense()
-            Xp = torch.from_numpy(Xh).pin_memory().numpy()
-            del Xh
-            yp = torch.from_numpy(yh).pin_memory().numpy()
-            h2d = n * (d + 1) * 8
-            # page-locked buffers: the library DMAs straight from them on its copy stream, so the ingest of
-            # step t+1 is issued before step t computes and overlaps it (streaming ingest)
-            make = (lambda: ctx.batch_from_dense(Xp, yp)) if args.e2e_sync else (lambda: ctx.batch_from_dense_async(Xp, yp))
-        model.setInitialWeights(tw.Vectors.zeros(d))
-        t_ingest = t_step = 0.0
-
-        def run(k):
-            nonlocal t_ingest, t_step
-            nxt = make()
-            for i in range(k):
-                b = nxt
-                t0 = time.perf_counter()
-                nxt = make() if i + 1 < k else None        # every step's rows cross PCIe inside the timed region
-                t1 = time.perf_counter()
-                st, _, _ = model.step(b, want_arrays=False)
-                w = model.latestModel().weights.toArray()
-                t_ingest += t1 - t0
-                t_step += time.perf_counter() - t1
-                b.free()
-            return st, w
-
-        run(1)
-        t_ingest = t_step = 0.0
-        barrier()
-        t0 = time.perf_counter()
-        st, w = run(args.e2e_steps)
-        barrier()
-        e2e_s = max_over_ranks(time.perf_counter() - t0)
-        e2e = {"value": world * n * iters * args.e2e_steps / e2e_s, "unit": UNIT,
-               "h2d_bytes_per_step": int(world * h2d),
-               "d2h_bytes_per_step": int(world * (d * 8 + iters * 8 + 80)),
-               "steps": args.e2e_steps, "ingest_ms_per_step": t_ingest / args.e2e_steps * 1e3,
-               "compute_ms_per_step": t_step / args.e2e_steps * 1e3,
-               "h2d_GBps_effective": h2d * args.e2e_steps / e2e_s / 1e9,
-               "includes": "host buffers -> HBM ingest (H2D%s), stats + %d iterations, weights/loss/stats back"
-                           % (" + transpose build" if csr else ", pinned, next step's copy overlapping this step's compute", iters)}
-
-    narrow = bool(csr) and d <= 2048 and not os.environ.get("TWTML_NO_NARROW")  # csr_narrow.cuh: kNarrowMaxD
-    if rank == 0:
-        peak, peak_src = measured_peak()
-        achieved = kbytes / (kern_ms_per_launch * 1e-3) / 1e9
-        traffic = None
-        try:
-            with open(os.path.join(ROOT, "profiles", "iter_kernel_traffic.json")) as f:
-                t = json.load(f)
-                for ent in (t if isinstance(t, list) else [t]):
-                    if ent.get("rows") == n and ent.get("features") == d and bool(ent.get("csr", False)) == bool(csr):
-                        traffic = ent["dram_bytes_per_launch"]
-        except Exception:
-            pass
-        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                "dtype": "f64", "data": "synthetic",
-                "config": {"workload": args.workload, "rows_per_gpu": n, "features": d, "sgd_iterations": iters,
-                           "convergence_tol": 0.0, **({"tweets_per_gpu": n_tweets, "nnz_per_gpu": batch.nnz} if tweets is not None else {}), "parallelism": "rows sharded x%d, one exchange of the shard partials per iteration" % world,
-                           "l2": ("inputs (%.3f GB/GPU) about the size of L2, fetched with an evict-first policy: ncu shows every launch reading them from HBM (profiles/); no flush"
-                                  % ((batch.nnz * 12 + n * 16) / 1e9)) if narrow else
-                                 "inputs (%.2f GB/GPU) larger than L2; no flush needed" % ((batch.nnz * 12 * 2 + n * 24) / 1e9 if csr else n * (d + 2) * 8 / 1e9),
-                           "timing": "CUDA events on the library stream around each step's iteration loop, max over ranks"},
-                "wall_ms_per_step": wall_ms / args.steps,
-                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": traffic, "peak_source": peak_src,
-                             "kernel": ("k_csr_narrow<TRAIN> (single pass over the CSR)" if narrow else "k_csr_rows + k_csc_windows + k_csc_edges (one read of the CSR credited)") if csr else ("k_dense_iter<1,TRAIN,RL1>" if d + 1 > 992 else "k_dense_iter<1,TRAIN,row lanes>"),
-                             "kernel_ms": kern_ms_per_launch, "bytes_per_launch": int(kbytes),
-                             "frac_of_nominal_8TBs": achieved / 8000.0},
-                "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
-                "exchange": ("none (1 GPU)" if world == 1 else (("NCCL all-to-all of gradient slices + all-gather of w, %d calls per step" if nccl_calls == 2 * iters else
-                                                                  "NCCL all-gather, %d calls per step") % nccl_calls if nccl_calls else
-                                                                "peer-memory stores + flags inside the reduce/update kernels (0 NCCL calls per step)"))}
-        if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"], _, _ = cpu_leg(wl, 3, 1)
+    bench = Bench(args)
+    e2e_steps = args.e2e_steps if args.e2e_steps >= 0 else (2 if (not wl.get("csr") and wl["rows"] > 4 * CHUNK_ROWS) else 8)
+    line = bench.run(args.workload, wl, args.steps, args.warmup, e2e_steps, sample_clocks=True)
+    subs = args.sub if args.sub is not None else (DEFAULT_SUBS if (args.gpus == 1 and args.workload == DEFAULT_WORKLOAD and not args.rows) else "none")
+    sub_records = {}
+    if subs != "none":
+        for name in [s for s in subs.split(",") if s and s != args.workload]:
+            swl = dict(WORKLOADS[name])
+            rec = bench.run(name, swl, 10, 3, 8, sample_clocks=False)
+            if rec is not None:
+                sub_records[name] = {k: rec[k] for k in ("value", "unit", "steps", "warmup", "ms_per_step", "config", "notes", "roofline", "e2e", "gpu_launches")}
+    bench.close()
+    if line is not None:
+        if sub_records:
+            line["sub_records"] = sub_records
+        if args.gpus == 1 and not args.no_cpu_baseline:
+            os.sched_setaffinity(0, full_affinity)               # the CPU leg uses every core of the box again
+            line["cpu_baseline"], _, _ = cpu_leg(wl, 3, 1, max_seconds=40.0)
         print(json.dumps(line), flush=True)
-    batch.free()
-    ctx.close()
-    if world > 1:
-        dist.destroy_process_group()
 
 
 if __name__ == "__main__":

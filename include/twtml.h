@@ -165,13 +165,45 @@ int32_t twtml_batch_from_dense(twtml_ctx* ctx, int64_t n, int64_t d, const doubl
 /* The same, returning while the rows are still on their way: the copy runs on the library's copy
  * stream and overlaps whatever the context is computing, which is how batch t+1 is ingested under
  * the SGD of batch t (north_star: "packed once into pinned host memory and copied asynchronously";
- * the reference's receiver likewise fills the next RDD while foreachRDD works on the current one).
- * X and labels must be page-locked host memory and stay untouched until the batch has been used by
- * a compute call or twtml_batch_ready(b, 1, ..) has returned; with pageable memory, or on a
- * multi-rank context, the call simply behaves like twtml_batch_from_dense. */
+ * the reference's receiver likewise fills the next RDD while foreachRDD works on the current one,
+ * LinearRegression.scala:44-47,53,86).  X and labels must be page-locked host memory and stay
+ * untouched until the batch has been used by a compute call or twtml_batch_ready(b, 1, ..) has
+ * returned; with pageable memory the call simply behaves like twtml_batch_from_dense.  Works on
+ * multi-rank contexts too: the ranks' row counts are then exchanged at the batch's first use (every
+ * rank must use its batches in the same order, as with any collective). */
 int32_t twtml_batch_from_dense_async(twtml_ctx* ctx, int64_t n, int64_t d, const double* X, int64_t ld_x,
                                      const double* labels, twtml_batch** out);
-/* *ready = 1 once the batch's rows are in HBM; wait != 0 blocks until then. */
+
+/* A dense micro-batch that arrives in pieces -- the way a Spark Streaming receiver stores the blocks
+ * of one batch interval before the interval's RDD exists (TwitterUtils.createStream ...,
+ * LinearRegression.scala:44).  _begin reserves HBM for n rows of d features; every _append copies the
+ * next nrows rows (same conventions as twtml_batch_from_dense_async: asynchronous from page-locked
+ * memory, which must stay untouched until twtml_batch_ready(b, 1, ..) returns; staged and blocking
+ * from pageable memory).  The batch can be used once all n rows have been appended.  A host can thus
+ * stream a batch far larger than its own page-locked buffer (2^24 x 1004 rows are 135 GB). */
+int32_t twtml_batch_dense_begin(twtml_ctx* ctx, int64_t n, int64_t d, twtml_batch** out);
+int32_t twtml_batch_dense_append(twtml_batch* b, int64_t nrows, const double* X, int64_t ld_x,
+                                 const double* labels);
+
+/* twtml_batch_from_csr / twtml_batch_from_tweets that return at once: validation, copies, the
+ * featuriser and the transpose of wide models run on a worker thread of the context and on its copy
+ * stream, beside whatever the context computes (same reference behaviour as above: the receiver fills
+ * the RDD of interval t+1 while foreachRDD works on interval t).  The caller's arrays must stay
+ * untouched until the batch has been used by a compute call or twtml_batch_ready(b, 1, ..) has
+ * returned.  twtml_batch_rows is valid at once (for tweets the host applies MllibHelper.filtrate
+ * itself); twtml_batch_info's nnz waits for the featuriser.  A failure of the deferred work is
+ * reported by the first call that uses the batch.  Bit-identical to the blocking calls. */
+int32_t twtml_batch_from_csr_async(twtml_ctx* ctx, int64_t n, int64_t d, const int64_t* rowptr,
+                                   const int32_t* colidx, const double* vals, const double* labels,
+                                   twtml_batch** out);
+int32_t twtml_batch_from_tweets_async(twtml_ctx* ctx, const uint16_t* text_utf16, const int64_t* text_off,
+                                      const int32_t* retweet_cnt, const int32_t* followers,
+                                      const int32_t* favourites, const int32_t* friends,
+                                      const int64_t* created_ms, const uint8_t* is_retweet, int64_t n,
+                                      int64_t now_ms, int32_t rt_begin, int32_t rt_end,
+                                      int32_t num_text_features, uint32_t flags, twtml_batch** out);
+/* *ready = 1 once the batch's rows (all that were appended so far) are in HBM; wait != 0 blocks
+ * until then. */
 int32_t twtml_batch_ready(const twtml_batch* b, int32_t wait, int32_t* ready);
 
 /* Synthetic micro-batches generated in HBM (measurement tool for SURVEY.md 8d configs 2-5; no

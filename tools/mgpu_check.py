@@ -86,8 +86,62 @@ def main():
             assert np.max(np.abs(mw.lastLossHistory - hw_ref) / np.abs(hw_ref)) < 1e-6
             wt2 = torch.from_numpy(ww).cuda(); w0t2 = wt2.clone(); dist.broadcast(w0t2, src=0)
             assert torch.equal(wt2, w0t2), "ranks disagree on the wide weights"
+    # ---- the exchange buffer's two parities across calls: train twice on one resident batch with tolerances that make
+    # the first call stop after an odd, then after an even number of exchanges; no collective sits between the calls, so a
+    # sequence number that counted enqueued (rather than executed) exchanges would let a fast rank overwrite a parity a
+    # slow one is still reading.  Weights must equal the oracle's and be the same bits on every rank, every round.
+    n, d = 8 * 64, 16
+    X, y = oracle_c.synth_dense(n, d, seed=3)
+    lo, hi = row_range(n, rank, world)
+    b = ctx.batch_from_dense(X[lo:hi], y[lo:hi])
+    for tol, step in [(0.5, 0.1), (0.02, 0.1), (0.5, 0.3), (0.1, 0.05), (0.0, 0.1)]:
+        w_ref = np.zeros(d)
+        m = (tw.StreamingLinearRegressionWithSGD(ctx=ctx).setNumIterations(9).setStepSize(step)
+             .setConvergenceTol(tol).setInitialWeights(tw.Vectors.zeros(d)))
+        ran = []
+        for call in range(4):
+            m.trainOnBatch(b)
+            w_ref, h_ref = oracle_c.sgd(y, d, w_ref, X=X, step_size=step, num_iterations=9, convergence_tol=tol)
+            ran.append(len(h_ref))
+            assert len(m.lastLossHistory) == len(h_ref), (tol, call, len(m.lastLossHistory), len(h_ref))
+            w = m.latestModel().weights.toArray()
+            assert np.max(np.abs(w - w_ref)) <= 1e-9 * max(1.0, np.max(np.abs(w_ref)))
+            wt = torch.from_numpy(w).cuda(); w0t = wt.clone(); dist.broadcast(w0t, src=0)
+            assert torch.equal(wt, w0t), "ranks disagree after repeated calls"
+        results[("rep%g_%g" % (tol, step), 0)] = np.array(ran, np.float64)
+    b.free()
+    # ---- asynchronous ingest on a ranked context: page-locked rows, the row-count exchange deferred to first use
+    n, d = 8 * 500, 1004
+    X, y = oracle_c.synth_dense(n, d, seed=8)
+    lo, hi = row_range(n, rank, world)
+    Xp = torch.from_numpy(np.ascontiguousarray(X[lo:hi])).pin_memory().numpy()
+    yp = torch.from_numpy(np.ascontiguousarray(y[lo:hi])).pin_memory().numpy()
+    ws = []
+    for make in (lambda: ctx.batch_from_dense(Xp, yp), lambda: ctx.batch_from_dense_async(Xp, yp)):
+        m = (tw.StreamingLinearRegressionWithSGD(ctx=ctx).setNumIterations(6).setStepSize(0.1).setMiniBatchFraction(0.5)
+             .setConvergenceTol(0.0).setInitialWeights(tw.Vectors.zeros(d)))
+        bb = make()
+        st, _, _ = m.step(bb)
+        assert st["batch"] == n
+        ws.append(m.latestModel().weights.toArray())
+        bb.free()
+    assert np.array_equal(ws[0], ws[1]), "asynchronous ingest changed the result"
+    w_ref, _ = oracle_c.sgd(y, d, np.zeros(d), X=X, step_size=0.1, num_iterations=6, mini_batch_fraction=0.5, convergence_tol=0.0)
+    assert np.max(np.abs(ws[1] - w_ref)) / np.max(np.abs(w_ref)) < 1e-6        # the sampler saw the right global row numbers
+    rp, ci, va, la = oracle_c.synth_csr(n, 1000, seed=12)
+    parts = (rp[lo:hi + 1] - rp[lo], ci[rp[lo]:rp[hi]], va[rp[lo]:rp[hi]], la[lo:hi])
+    ws = []
+    for wait in (True, False):
+        m = (tw.StreamingLinearRegressionWithSGD(ctx=ctx).setNumIterations(5).setStepSize(0.005)
+             .setConvergenceTol(0.0).setInitialWeights(tw.Vectors.zeros(1004)))
+        bb = ctx.batch_from_csr(hi - lo, 1004, *parts, wait=wait)
+        m.trainOnBatch(bb)
+        ws.append(m.latestModel().weights.toArray())
+        bb.free()
+    assert np.array_equal(ws[0], ws[1]), "asynchronous CSR ingest changed the result"
+    results[("async", 0)] = ws[1]
     if rank == 0:
-        np.savez(os.environ.get("MGPU_OUT", "/tmp/mgpu_w%d.npz" % world), **{"%d_%d" % k: v for k, v in results.items()})
+        np.savez(os.environ.get("MGPU_OUT", "/tmp/mgpu_w%d.npz" % world), **{"%s_%s" % k: v for k, v in results.items()})
         print("MGPU OK world=%d" % world, flush=True)
     ctx.close()
     dist.destroy_process_group()

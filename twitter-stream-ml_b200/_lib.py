@@ -95,6 +95,10 @@ SIGNATURES = {
     "twtml_batch_from_csr": [_vp, _i64, _i64, _vp, _vp, _vp, _vp, C.POINTER(_vp)],
     "twtml_batch_from_dense": [_vp, _i64, _i64, _vp, _i64, _vp, C.POINTER(_vp)],
     "twtml_batch_from_dense_async": [_vp, _i64, _i64, _vp, _i64, _vp, C.POINTER(_vp)],
+    "twtml_batch_dense_begin": [_vp, _i64, _i64, C.POINTER(_vp)],
+    "twtml_batch_dense_append": [_vp, _i64, _vp, _i64, _vp],
+    "twtml_batch_from_csr_async": [_vp, _i64, _i64, _vp, _vp, _vp, _vp, C.POINTER(_vp)],
+    "twtml_batch_from_tweets_async": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i32, _i32, _i32, _u32, C.POINTER(_vp)],
     "twtml_batch_ready": [_vp, _i32, C.POINTER(_i32)],
     "twtml_batch_synth_dense": [_vp, _i64, _i64, _u64, _i64, C.POINTER(_vp)],
     "twtml_batch_synth_csr": [_vp, _i64, _i32, _u64, _i64, C.POINTER(_vp)],

@@ -89,23 +89,47 @@ class Context:
         b._keep = (X, labels)
         return b
 
-    def batch_from_csr(self, n, d, rowptr, colidx, vals, labels):
+    def batch_dense_begin(self, n, d):
+        """A dense batch of n rows whose rows arrive with Batch.append(X, labels), piece by piece (the blocks a
+        receiver stores during one batch interval); usable once all n rows are in."""
+        h = C.c_void_p()
+        check(_lib.lib().twtml_batch_dense_begin(self._h, n, d, C.byref(h)))
+        b = Batch(self, h)
+        b._keep = []
+        return b
+
+    def batch_from_csr(self, n, d, rowptr, colidx, vals, labels, wait=True):
+        """wait=False: twtml_batch_from_csr_async -- returns at once, the ingest runs beside the context's compute."""
         rowptr, colidx = _lib.arr(rowptr, np.int64), _lib.arr(colidx, np.int32)
         vals, labels = _lib.arr(vals, np.float64), _lib.arr(labels, np.float64)
         h = C.c_void_p()
-        check(_lib.lib().twtml_batch_from_csr(self._h, n, d, ptr(rowptr), ptr(colidx), ptr(vals), ptr(labels), C.byref(h)))
-        return Batch(self, h)
+        fn = _lib.lib().twtml_batch_from_csr if wait else _lib.lib().twtml_batch_from_csr_async
+        check(fn(self._h, n, d, ptr(rowptr), ptr(colidx), ptr(vals), ptr(labels), C.byref(h)))
+        b = Batch(self, h)
+        if not wait:
+            b._keep = (rowptr, colidx, vals, labels)
+        return b
 
-    def batch_from_tweets(self, tweets, now_ms, rt_begin=100, rt_end=1000, num_text_features=1000, lowercase=False):
-        """tweets: TweetBatch (struct of arrays).  Filter + featurise on the GPU."""
+    def batch_from_csr_async(self, n, d, rowptr, colidx, vals, labels):
+        return self.batch_from_csr(n, d, rowptr, colidx, vals, labels, wait=False)
+
+    def batch_from_tweets(self, tweets, now_ms, rt_begin=100, rt_end=1000, num_text_features=1000, lowercase=False, wait=True):
+        """tweets: TweetBatch (struct of arrays).  Filter + featurise on the GPU.  wait=False:
+        twtml_batch_from_tweets_async (the row count is known at once, nnz once the featuriser has run)."""
         t = tweets
         h = C.c_void_p()
         text = t.text_utf16 if t.text_utf16.size else np.zeros(1, np.uint16)
-        check(_lib.lib().twtml_batch_from_tweets(
-            self._h, ptr(text), ptr(t.text_off), ptr(t.retweet_count), ptr(t.followers), ptr(t.favourites),
-            ptr(t.friends), ptr(t.created_ms), ptr(t.is_retweet), len(t), int(now_ms), rt_begin, rt_end,
-            num_text_features, _lib.FLAG_LOWERCASE if lowercase else 0, C.byref(h)))
-        return Batch(self, h)
+        fn = _lib.lib().twtml_batch_from_tweets if wait else _lib.lib().twtml_batch_from_tweets_async
+        check(fn(self._h, ptr(text), ptr(t.text_off), ptr(t.retweet_count), ptr(t.followers), ptr(t.favourites),
+                 ptr(t.friends), ptr(t.created_ms), ptr(t.is_retweet), len(t), int(now_ms), rt_begin, rt_end,
+                 num_text_features, _lib.FLAG_LOWERCASE if lowercase else 0, C.byref(h)))
+        b = Batch(self, h)
+        if not wait:
+            b._keep = (text, t)
+        return b
+
+    def batch_from_tweets_async(self, tweets, now_ms, rt_begin=100, rt_end=1000, num_text_features=1000, lowercase=False):
+        return self.batch_from_tweets(tweets, now_ms, rt_begin, rt_end, num_text_features, lowercase, wait=False)
 
     def batch_synth_dense(self, n, d, seed=42, row0=0):
         h = C.c_void_p()
@@ -123,13 +147,33 @@ class Batch:
 
     def __init__(self, ctx, handle):
         self.ctx, self._h = ctx, handle
-        n, d, nnz, csr = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int32()
-        check(_lib.lib().twtml_batch_info(handle, C.byref(n), C.byref(d), C.byref(nnz), C.byref(csr)))
-        self.n, self.d, self.nnz, self.is_csr = n.value, d.value, nnz.value, bool(csr.value)
+        n, d, csr = C.c_int64(), C.c_int64(), C.c_int32()
+        check(_lib.lib().twtml_batch_info(handle, C.byref(n), C.byref(d), None, C.byref(csr)))
+        self.n, self.d, self.is_csr = n.value, d.value, bool(csr.value)
+        self._nnz = None
         ctx._children.add(self)
+
+    @property
+    def nnz(self):
+        """Stored entries; for an asynchronously featurised batch this waits for the featuriser."""
+        if self._nnz is None:
+            v = C.c_int64()
+            check(_lib.lib().twtml_batch_info(self._h, None, None, C.byref(v), None))
+            self._nnz = v.value
+        return self._nnz
 
     def count(self):
         return self.n
+
+    def append(self, X, labels):
+        """Next rows of a batch from Context.batch_dense_begin (twtml_batch_dense_append)."""
+        X = np.asarray(X, np.float64)
+        labels = np.ascontiguousarray(labels, np.float64)
+        if X.ndim != 2 or X.shape[0] != labels.shape[0] or X.shape[1] != self.d or X.strides[1] != 8 or X.strides[0] % 8:
+            raise ValueError("X must be nrows x d float64 with unit column stride and one label per row")
+        check(_lib.lib().twtml_batch_dense_append(self._h, X.shape[0], ptr(X), X.strides[0] // 8 if X.shape[0] > 1 else X.shape[1], ptr(labels)))
+        self._keep.append((X, labels))
+        return self
 
     def ready(self, wait=False):
         r = C.c_int32()

@@ -69,6 +69,8 @@ __host__ __device__ inline int narrow_warps(int d)
     const long long w = room / (8ll * (d > 0 ? d : 1));
     return (int)(w > kNarrowMaxWarps ? kNarrowMaxWarps : w);
 }
+// resident CTAs of the single-pass kernel per SM (the grid at ingest is sized to this)
+__host__ __device__ inline int narrow_ctas_per_sm(int d) { (void)d; return 1; }
 __host__ __device__ inline size_t narrow_smem_bytes(int d, int warps)
 {
     return kNarrowRingBytes + (size_t)8 * d + 8 * kNarrowRedDoubles + (size_t)8 * d * warps;

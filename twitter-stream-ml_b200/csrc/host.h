@@ -3,8 +3,14 @@
 #include <cuda_runtime.h>
 #include <nccl.h> // types only: libnccl is dlopen'ed at run time (nccl_dyn.h), never linked
 
+#include <atomic>
+#include <condition_variable>
+#include <deque>
+#include <functional>
+#include <future>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/twtml.h"
@@ -38,6 +44,22 @@ struct DevBuf {
     template <class T> T* as() const { return static_cast<T*>(p); }
 };
 
+// Everything one ingest needs besides the batch it fills: a stream and the scratch that goes with it.  A context has
+// two lanes so that the ingest of micro-batch t+1 never shares a buffer with the compute (or the ingest) of batch t:
+// lane 0 works on the compute stream for the blocking twtml_batch_from_* calls, lane 1 on the copy stream for the
+// *_async ones.
+struct IngestLane {
+    std::mutex mu;                             // held while work is being enqueued on the lane (caller thread or the ingest worker)
+    cudaStream_t stream = nullptr;
+    DevBuf scan_tmp, sort_tmp;                 // CUB temporaries (prefix sums, the transpose's radix sort)
+    DevBuf labels_tmp;                         // labels on their way into a dense batch's label column
+    DevBuf stage;                              // flat landing zone of page-locked dense rows (two halves)
+    cudaEvent_t stage_ev[2][2] = {};           // [half][0: chunk copied, 1: chunk spread]
+    void* pin[2] = {nullptr, nullptr};         // pinned staging ring for pageable caller memory
+    size_t pin_bytes = 0;
+    cudaEvent_t pin_ev[2] = {nullptr, nullptr};
+};
+
 } // namespace twtml
 
 struct twtml_ctx {
@@ -49,7 +71,7 @@ struct twtml_ctx {
     cudaMemPool_t pool = nullptr;       // batch memory: stream-ordered, kept across batches (no OS round trip, no device-wide sync)
     ncclComm_t comm = nullptr;
     std::mutex mu;
-    int live_handles = 0; // models + batches created on this context and not yet freed
+    std::atomic<int> live_handles{0}; // models + batches created on this context and not yet freed
     // peer-memory exchange of the shard vectors (reduce.cuh PeerExchange); falls back to NCCL when not set up
     bool p2p_ok = false;
     double* xbuf = nullptr;                 // this rank's exchange buffer
@@ -60,13 +82,15 @@ struct twtml_ctx {
     unsigned smem_attr_done = 0; // dense iteration-kernel forms whose dynamic shared-memory limit is raised
     // scratch, reused across calls
     twtml::DevBuf partials, shards, stat_partials, stat_shards, state, loss_hist, out10, tmp_a, tmp_b, gather, lower, upd_parts, slices, wprev;
-    twtml::DevBuf stage[2]; // flat landing zone of pinned dense ingest: [0] compute stream, [1] copy stream
+    twtml::IngestLane lane[2];                 // [0] blocking ingest on the compute stream, [1] asynchronous ingest on the copy stream
     cudaStream_t spread_stream = nullptr;      // k_repitch runs here, beside the next chunk's copy
-    cudaEvent_t stage_ev[2][2][2] = {};        // [landing zone][half][0: chunk copied, 1: chunk spread]
-    // pinned staging ring for host -> device ingest
-    void* pin[2] = {nullptr, nullptr};
-    size_t pin_bytes = 0;
-    cudaEvent_t pin_ev[2] = {nullptr, nullptr};
+    // asynchronous CSR / tweet ingest: jobs run in order on one worker thread per context (started on first use), so the
+    // host-side waits an ingest needs (sizes that only the device knows) never block the thread that drives the compute
+    std::thread worker;
+    std::mutex qmu;
+    std::condition_variable qcv;
+    std::deque<std::function<void()>> jobs;
+    bool worker_stop = false;
     // profiling
     bool profiling = false;
     std::vector<cudaEvent_t> ev;
@@ -89,6 +113,13 @@ struct twtml_batch {
     int64_t n = 0, d = 0, nnz = 0;
     int64_t n_global = 0, row0_global = 0;
     cudaEvent_t ready = nullptr; // set by asynchronous ingest: recorded on the copy stream when the rows are in HBM
+    // asynchronous ingest through the context's worker thread (CSR, tweets): the job's verdict; fields below n / d are
+    // the worker's until it is in
+    std::shared_future<int> pending;
+    bool has_pending = false;
+    std::string pending_err;
+    bool global_deferred = false; // multi-rank: n_global / row0_global still to be exchanged (done at first use, on the compute stream)
+    int64_t rows_appended = 0;    // twtml_batch_dense_begin / _append: rows delivered so far
     // dense
     double* X = nullptr;
     int64_t ldx = 0;
@@ -117,13 +148,16 @@ struct twtml_batch {
 
 namespace twtml {
 // shared between twtml.cu and twtml_sparse.cu
-int upload_plain(twtml_ctx* ctx, void* dst, const void* src, size_t bytes);
+int upload_plain(twtml_ctx* ctx, IngestLane& lane, void* dst, const void* src, size_t bytes);
+const char* last_error_text();
+int submit_ingest(twtml_ctx* ctx, twtml_batch* b, std::function<int()> job);
+int settle_batch(twtml_ctx* ctx, const twtml_batch* b);
 int ctx_global_rows(twtml_ctx* ctx, int64_t n_local, int64_t* n_global, int64_t* row0);
 void make_plan(int64_t n_local, int spr, int R, Plan& p, int64_t min_blocks = 64);
 void batch_free_locked(twtml_batch* b);
 // batch memory from the context's pool, ordered on the compute stream
-int pool_alloc(twtml_ctx* ctx, void** p, size_t bytes);
-void pool_free(twtml_ctx* ctx, void* p);
+int pool_alloc(twtml_ctx* ctx, void** p, size_t bytes, cudaStream_t stream = nullptr);
+void pool_free(twtml_ctx* ctx, void* p, cudaStream_t stream = nullptr);
 // launch shape of the dense iteration kernel for a feature width
 struct DenseCfg {
     int cp, c2, c2p, rl, R, nstages, grid_per_sm;

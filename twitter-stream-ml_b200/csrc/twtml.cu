@@ -6,6 +6,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <chrono>
 #include <cstring>
 #include <functional>
 #include <thread>
@@ -37,6 +38,8 @@ int fail(int code, const char* fmt, ...)
     va_end(ap);
     return code;
 }
+
+const char* last_error_text() { return g_err; }
 
 int DevBuf::reserve(size_t bytes)
 {
@@ -264,16 +267,17 @@ int ctx_global_rows(twtml_ctx* ctx, int64_t n_local, int64_t* n_global, int64_t*
     return 0;
 }
 
-int pool_alloc(twtml_ctx* ctx, void** p, size_t bytes)
+int pool_alloc(twtml_ctx* ctx, void** p, size_t bytes, cudaStream_t stream)
 {
     *p = nullptr;
     if (bytes == 0) bytes = 8;
-    cudaError_t e = cudaMallocFromPoolAsync(p, bytes, ctx->pool, ctx->stream);
+    if (!stream) stream = ctx->stream;
+    cudaError_t e = cudaMallocFromPoolAsync(p, bytes, ctx->pool, stream);
     if (e != cudaSuccess) { // give cached blocks back and try once more
         cudaGetLastError();
-        cudaStreamSynchronize(ctx->stream);
+        cudaStreamSynchronize(stream);
         cudaMemPoolTrimTo(ctx->pool, 0);
-        e = cudaMallocFromPoolAsync(p, bytes, ctx->pool, ctx->stream);
+        e = cudaMallocFromPoolAsync(p, bytes, ctx->pool, stream);
     }
     if (e != cudaSuccess) {
         *p = nullptr;
@@ -283,42 +287,42 @@ int pool_alloc(twtml_ctx* ctx, void** p, size_t bytes)
     return 0;
 }
 
-void pool_free(twtml_ctx* ctx, void* p)
+void pool_free(twtml_ctx* ctx, void* p, cudaStream_t stream)
 {
-    if (p) cudaFreeAsync(p, ctx->stream);
+    if (p) cudaFreeAsync(p, stream ? stream : ctx->stream);
 }
 
-static int ensure_pinned(twtml_ctx* ctx, size_t bytes)
+static int ensure_pinned(IngestLane& lane, size_t bytes)
 {
-    if (ctx->pin_bytes >= bytes) return 0;
+    if (lane.pin_bytes >= bytes) return 0;
     for (int i = 0; i < 2; ++i) {
-        if (ctx->pin[i]) cudaFreeHost(ctx->pin[i]);
-        ctx->pin[i] = nullptr;
+        if (lane.pin[i]) { cudaEventSynchronize(lane.pin_ev[i]); cudaFreeHost(lane.pin[i]); }
+        lane.pin[i] = nullptr;
     }
-    ctx->pin_bytes = 0;
-    for (int i = 0; i < 2; ++i) TW_CUDA(cudaMallocHost(&ctx->pin[i], bytes));
-    ctx->pin_bytes = bytes;
+    lane.pin_bytes = 0;
+    for (int i = 0; i < 2; ++i) TW_CUDA(cudaMallocHost(&lane.pin[i], bytes));
+    lane.pin_bytes = bytes;
     return 0;
 }
 
 // Host -> device in chunks through the two pinned buffers: chunk k+1 is packed by `pack` while chunk
 // k is in flight.  pack(dst, first_unit, n_units) fills dst with n_units * unit_bytes bytes.
 template <class PackFn>
-int staged_upload(twtml_ctx* ctx, void* dst, size_t unit_bytes, int64_t n_units, PackFn pack)
+int staged_upload(IngestLane& lane, void* dst, size_t unit_bytes, int64_t n_units, PackFn pack)
 {
     if (n_units <= 0) return 0;
     const size_t chunk_bytes = (size_t)32 << 20;
-    TW_TRY(ensure_pinned(ctx, std::max(chunk_bytes, unit_bytes)));
-    const int64_t per = std::max<int64_t>(1, (int64_t)(ctx->pin_bytes / unit_bytes));
+    TW_TRY(ensure_pinned(lane, std::max(chunk_bytes, unit_bytes)));
+    const int64_t per = std::max<int64_t>(1, (int64_t)(lane.pin_bytes / unit_bytes));
     int k = 0;
     for (int64_t u0 = 0; u0 < n_units; u0 += per, ++k) {
         const int64_t nu = std::min(per, n_units - u0);
         const int bi = k & 1;
-        TW_CUDA(cudaEventSynchronize(ctx->pin_ev[bi])); // the last copy out of this buffer (maybe an earlier call's) is done
-        pack(static_cast<char*>(ctx->pin[bi]), u0, nu);
-        TW_CUDA(cudaMemcpyAsync(static_cast<char*>(dst) + (size_t)u0 * unit_bytes, ctx->pin[bi], (size_t)nu * unit_bytes,
-                                cudaMemcpyHostToDevice, ctx->stream));
-        TW_CUDA(cudaEventRecord(ctx->pin_ev[bi], ctx->stream));
+        TW_CUDA(cudaEventSynchronize(lane.pin_ev[bi])); // the last copy out of this buffer (maybe an earlier call's) is done
+        pack(static_cast<char*>(lane.pin[bi]), u0, nu);
+        TW_CUDA(cudaMemcpyAsync(static_cast<char*>(dst) + (size_t)u0 * unit_bytes, lane.pin[bi], (size_t)nu * unit_bytes,
+                                cudaMemcpyHostToDevice, lane.stream));
+        TW_CUDA(cudaEventRecord(lane.pin_ev[bi], lane.stream));
     }
     return 0;
 }
@@ -327,15 +331,16 @@ static bool page_locked(const void* p);
 
 // Host -> device copy of a plain array: straight DMA when the caller's memory is page-locked, else through
 // the pinned ring with the staging memcpy spread over host threads.
-int upload_plain(twtml_ctx* ctx, void* dst, const void* src, size_t bytes)
+int upload_plain(twtml_ctx* ctx, IngestLane& lane, void* dst, const void* src, size_t bytes)
 {
+    (void)ctx;
     if (bytes == 0) return 0;
     if (page_locked(src)) {
-        TW_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+        TW_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, lane.stream));
         return 0;
     }
     const char* s = static_cast<const char*>(src);
-    return staged_upload(ctx, dst, 1, (int64_t)bytes, [s](char* out, int64_t u0, int64_t nu) {
+    return staged_upload(lane, dst, 1, (int64_t)bytes, [s](char* out, int64_t u0, int64_t nu) {
         parallel_rows(nu, 4 << 20, [&](int64_t lo, int64_t hi) { memcpy(out + lo, s + u0 + lo, (size_t)(hi - lo)); });
     });
 }
@@ -380,42 +385,45 @@ __global__ void k_repitch(const double* __restrict__ flat, double* __restrict__ 
 
 // Page-locked, densely packed host rows -> the batch's pitched rows.  A pitched (2-D) copy of 8 KB rows reaches ~45 GB/s
 // on this link, a flat one ~55 GB/s: so the rows land flat in a small device buffer (two halves, alternating) and a kernel
-// spreads each chunk to the row pitch and drops the labels in.  The copies are ordered on `stream`; the kernels run on the
-// context's spread stream, beside the next chunk's copy (events per half: copied -> spread -> may be overwritten); `stream`
-// ends up waiting for the last kernel, so whatever the caller orders after this call on `stream` sees the whole batch.
+// spreads each chunk to the row pitch and drops the labels in.  The copies are ordered on the lane's stream; the kernels run
+// on the context's spread stream, beside the next chunk's copy (events per half: copied -> spread -> may be overwritten); the
+// lane's stream ends up waiting for the last kernel, so whatever is ordered after this call on it sees all the rows.
+// Rows [row_begin, row_begin + nrows) of batch b; X and labels_dev point at the first of them.
 static const size_t kStageChunkBytes = (size_t)64 << 20;
-static cudaError_t flat_dense_ingest(twtml_ctx* ctx, int which, cudaStream_t stream, twtml_batch* b, const double* X, const double* labels_dev)
+static cudaError_t flat_dense_ingest(twtml_ctx* ctx, IngestLane& lane, twtml_batch* b, int64_t row_begin, int64_t nrows, const double* X,
+                                     const double* labels_dev)
 {
-    const int64_t n = b->n, d = b->d;
+    const int64_t n = nrows, d = b->d;
+    cudaStream_t stream = lane.stream;
     const int64_t rows_per = std::max<int64_t>(1, (int64_t)(kStageChunkBytes / (sizeof(double) * (size_t)d)));
     const size_t half = sizeof(double) * (size_t)rows_per * (size_t)d;
     const size_t need = n <= rows_per ? sizeof(double) * (size_t)n * (size_t)d : 2 * half; // a small batch uses one half only
-    if (ctx->stage[which].reserve(need)) return cudaErrorMemoryAllocation;
+    if (lane.stage.reserve(need)) return cudaErrorMemoryAllocation; // (growing it goes through cudaFree, which waits for the device)
     cudaStream_t spread = ctx->spread_stream;
     cudaError_t e;
     // the labels (copied on `stream` before this call) and, for a zone used before, its last kernels: order the spread stream
     // behind `stream` once; every kernel below additionally waits for its own chunk's copy
-    if ((e = cudaEventRecord(ctx->stage_ev[which][0][0], stream)) != cudaSuccess) return e;
-    if ((e = cudaStreamWaitEvent(spread, ctx->stage_ev[which][0][0], 0)) != cudaSuccess) return e;
+    if ((e = cudaEventRecord(lane.stage_ev[0][0], stream)) != cudaSuccess) return e;
+    if ((e = cudaStreamWaitEvent(spread, lane.stage_ev[0][0], 0)) != cudaSuccess) return e;
     int k = 0;
     int64_t chunk = 0;
     for (int64_t r0 = 0; r0 < n; r0 += rows_per, k ^= 1, ++chunk) {
         const int64_t nr = std::min(rows_per, n - r0);
-        double* st = reinterpret_cast<double*>(static_cast<char*>(ctx->stage[which].p) + (size_t)k * half);
+        double* st = reinterpret_cast<double*>(static_cast<char*>(lane.stage.p) + (size_t)k * half);
         // this half was last read by the kernel of chunk - 2
-        if (chunk >= 2 && (e = cudaStreamWaitEvent(stream, ctx->stage_ev[which][k][1], 0)) != cudaSuccess) return e;
+        if (chunk >= 2 && (e = cudaStreamWaitEvent(stream, lane.stage_ev[k][1], 0)) != cudaSuccess) return e;
         if ((e = cudaMemcpyAsync(st, X + r0 * d, sizeof(double) * (size_t)nr * (size_t)d, cudaMemcpyHostToDevice, stream)) != cudaSuccess) return e;
-        if ((e = cudaEventRecord(ctx->stage_ev[which][k][0], stream)) != cudaSuccess) return e;
-        if ((e = cudaStreamWaitEvent(spread, ctx->stage_ev[which][k][0], 0)) != cudaSuccess) return e;
+        if ((e = cudaEventRecord(lane.stage_ev[k][0], stream)) != cudaSuccess) return e;
+        if ((e = cudaStreamWaitEvent(spread, lane.stage_ev[k][0], 0)) != cudaSuccess) return e;
         const long long total = nr * b->ldx;
         const unsigned grid = (unsigned)std::min<long long>((total + 255) / 256, (long long)ctx->sm_count * 16);
-        k_repitch<<<grid, 256, 0, spread>>>(st, b->X + r0 * b->ldx, b->ldx, (int)d, labels_dev + r0, nr);
+        k_repitch<<<grid, 256, 0, spread>>>(st, b->X + (row_begin + r0) * b->ldx, b->ldx, (int)d, labels_dev + r0, nr);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
-        if ((e = cudaEventRecord(ctx->stage_ev[which][k][1], spread)) != cudaSuccess) return e;
+        if ((e = cudaEventRecord(lane.stage_ev[k][1], spread)) != cudaSuccess) return e;
     }
-    // both halves' last kernels before anything later on `stream` (the next batch's copies into this zone included)
+    // both halves' last kernels before anything later on `stream` (the next rows' copies into this zone included)
     for (int h = 0; h < 2; ++h)
-        if (chunk > h && (e = cudaStreamWaitEvent(stream, ctx->stage_ev[which][h][1], 0)) != cudaSuccess) return e;
+        if (chunk > h && (e = cudaStreamWaitEvent(stream, lane.stage_ev[h][1], 0)) != cudaSuccess) return e;
     return cudaSuccess;
 }
 
@@ -610,9 +618,77 @@ static int reduce_stats(twtml_ctx* ctx, const twtml_batch* b)
     return 0;
 }
 
-// a batch from twtml_batch_from_dense_async may still be in flight on the copy stream
+// ---- asynchronous ingest: the worker thread ---------------------------------------------------------
+static void worker_main(twtml_ctx* ctx)
+{
+    cudaSetDevice(ctx->device);
+    for (;;) {
+        std::function<void()> job;
+        {
+            std::unique_lock<std::mutex> lk(ctx->qmu);
+            ctx->qcv.wait(lk, [&] { return ctx->worker_stop || !ctx->jobs.empty(); });
+            if (ctx->jobs.empty()) return; // stop requested and nothing left to do
+            job = std::move(ctx->jobs.front());
+            ctx->jobs.pop_front();
+        }
+        job();
+    }
+}
+
+// Queue `job` (the ingest of batch b on lane 1) behind the context's earlier asynchronous ingests.  Its status
+// and message end up in b->pending / b->pending_err; the first call that uses the batch collects them.
+int submit_ingest(twtml_ctx* ctx, twtml_batch* b, std::function<int()> job)
+{
+    auto task = std::make_shared<std::packaged_task<int()>>([b, job]() {
+        const int rc = job();
+        if (rc) b->pending_err = last_error_text();
+        return rc;
+    });
+    b->pending = task->get_future().share();
+    b->has_pending = true;
+    {
+        std::lock_guard<std::mutex> lk(ctx->qmu);
+        if (!ctx->worker.joinable()) ctx->worker = std::thread(worker_main, ctx);
+        ctx->jobs.emplace_back([task]() { (*task)(); });
+    }
+    ctx->qcv.notify_one();
+    return 0;
+}
+
+static void stop_worker(twtml_ctx* ctx)
+{
+    {
+        std::lock_guard<std::mutex> lk(ctx->qmu);
+        ctx->worker_stop = true;
+    }
+    ctx->qcv.notify_all();
+    if (ctx->worker.joinable()) ctx->worker.join();
+}
+
+// Host side of "is this batch usable": the worker's verdict for an asynchronously ingested batch (blocks until it is
+// in), the rows of a batch that is being appended to, and -- on a multi-rank context -- the row-count exchange an
+// asynchronous ingest left for later (it is a collective on the compute stream: every rank gets here with the same
+// batch in the same order, exactly as they all reach the training loop that follows).
+int settle_batch(twtml_ctx* ctx, const twtml_batch* cb)
+{
+    twtml_batch* b = const_cast<twtml_batch*>(cb);
+    if (b->has_pending) {
+        const int rc = b->pending.get();
+        if (rc) return fail(rc, "asynchronous ingest failed: %s", b->pending_err.c_str());
+    }
+    if (!b->csr && b->rows_appended < b->n)
+        return fail(TWTML_E_INVALID_ARG, "batch used before all of its rows were appended (%lld of %lld)", (long long)b->rows_appended, (long long)b->n);
+    if (b->global_deferred) {
+        TW_TRY(ctx_global_rows(ctx, b->n, &b->n_global, &b->row0_global));
+        b->global_deferred = false;
+    }
+    return 0;
+}
+
+// ... and the device side: a batch ingested asynchronously may still be in flight on the copy stream
 static int wait_ready(twtml_ctx* ctx, const twtml_batch* b)
 {
+    TW_TRY(settle_batch(ctx, b));
     if (b->ready) TW_CUDA(cudaStreamWaitEvent(ctx->stream, b->ready, 0));
     return 0;
 }
@@ -637,8 +713,8 @@ static int fetch_rows(twtml_ctx* ctx, double* host, const double* dev, int64_t n
 static int do_predict_stats(const twtml_model* m, const twtml_batch* b, double* out_real, double* out_pred, twtml_stats* out)
 {
     twtml_ctx* ctx = m->ctx;
-    if (b->n_global == 0) { stats_empty(out); return 0; }
     TW_TRY(wait_ready(ctx, b));
+    if (b->n_global == 0) { stats_empty(out); return 0; }
     TW_TRY(reserve_scratch(ctx, m, b));
     double *dp = nullptr, *dr = nullptr;
     if (out_pred) { TW_TRY(ctx->tmp_a.reserve(sizeof(double) * (size_t)std::max<int64_t>(1, b->n))); dp = ctx->tmp_a.as<double>(); }
@@ -660,11 +736,11 @@ static int do_train(twtml_model* m, const twtml_batch* b, bool with_stats, doubl
     twtml_ctx* ctx = m->ctx;
     if (iters_run) *iters_run = 0;
     ctx->prof = twtml_profile{};
+    TW_TRY(wait_ready(ctx, b));
     if (b->n_global == 0) { // rdd.isEmpty: both output ops skip the batch
         if (with_stats && out) stats_empty(out);
         return 0;
     }
-    TW_TRY(wait_ready(ctx, b));
     TW_TRY(reserve_scratch(ctx, m, b));
     double *dp = nullptr, *dr = nullptr;
     if (with_stats && out_pred) { TW_TRY(ctx->tmp_a.reserve(sizeof(double) * (size_t)std::max<int64_t>(1, b->n))); dp = ctx->tmp_a.as<double>(); }
@@ -770,6 +846,7 @@ static int do_train(twtml_model* m, const twtml_batch* b, bool with_stats, doubl
 // caller holds the context lock (or is the only owner)
 void batch_free_locked(twtml_batch* b)
 {
+    if (b->has_pending) b->pending.wait(); // the worker still owns its fields
     if (b->ready) {
         cudaEventSynchronize(b->ready); // its own copy only; later batches may still be arriving
         cudaEventDestroy(b->ready);
@@ -828,9 +905,13 @@ static int32_t create_common(int32_t device, int32_t rank, int32_t world, const 
     if (se != cudaSuccess) { delete c; return fail(TWTML_E_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(se)); }
     cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
     cudaStreamCreateWithFlags(&c->spread_stream, cudaStreamNonBlocking);
-    for (auto& zone : c->stage_ev)
-        for (auto& half : zone)
+    c->lane[0].stream = c->stream;
+    c->lane[1].stream = c->copy_stream;
+    for (auto& lane : c->lane) {
+        for (auto& half : lane.stage_ev)
             for (auto& ev : half) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+        for (auto& ev : lane.pin_ev) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+    }
     {
         cudaMemPoolProps props{};
         props.allocType = cudaMemAllocationTypePinned;
@@ -841,7 +922,6 @@ static int32_t create_common(int32_t device, int32_t rank, int32_t world, const 
         unsigned long long keep = ~0ull; // freed batch memory stays cached for the next micro-batch
         cudaMemPoolSetAttribute(c->pool, cudaMemPoolAttrReleaseThreshold, &keep);
     }
-    for (int i = 0; i < 2; ++i) cudaEventCreateWithFlags(&c->pin_ev[i], cudaEventDisableTiming);
     if (cudaHostAlloc(reinterpret_cast<void**>(&c->host_done), sizeof(int), cudaHostAllocMapped) == cudaSuccess) {
         *c->host_done = 0;
         if (cudaHostGetDevicePointer(reinterpret_cast<void**>(&c->host_done_dev), c->host_done, 0) != cudaSuccess) c->host_done_dev = nullptr;
@@ -885,30 +965,35 @@ int32_t twtml_destroy(twtml_ctx* ctx)
     if (!ctx) return 0;
     {
         std::lock_guard<std::mutex> lk(ctx->mu);
-        if (ctx->live_handles != 0)
-            return fail(TWTML_E_INVALID_ARG, "twtml_destroy: %d models/batches of this context are still alive; free them first", ctx->live_handles);
+        if (ctx->live_handles.load() != 0)
+            return fail(TWTML_E_INVALID_ARG, "twtml_destroy: %d models/batches of this context are still alive; free them first", ctx->live_handles.load());
     }
+    stop_worker(ctx);
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
+    if (ctx->spread_stream) cudaStreamSynchronize(ctx->spread_stream);
     teardown_peer_exchange(ctx);
     if (ctx->host_done) cudaFreeHost(ctx->host_done);
     if (ctx->comm) nccl_api().CommDestroy(ctx->comm);
     for (DevBuf* b : {&ctx->partials, &ctx->shards, &ctx->stat_partials, &ctx->stat_shards, &ctx->state, &ctx->loss_hist, &ctx->out10,
-                      &ctx->tmp_a, &ctx->tmp_b, &ctx->gather, &ctx->lower, &ctx->upd_parts, &ctx->slices, &ctx->wprev, &ctx->stage[0], &ctx->stage[1]})
+                      &ctx->tmp_a, &ctx->tmp_b, &ctx->gather, &ctx->lower, &ctx->upd_parts, &ctx->slices, &ctx->wprev})
         b->release();
-    for (int i = 0; i < 2; ++i) {
-        if (ctx->pin[i]) cudaFreeHost(ctx->pin[i]);
-        if (ctx->pin_ev[i]) cudaEventDestroy(ctx->pin_ev[i]);
+    for (auto& lane : ctx->lane) {
+        for (DevBuf* b : {&lane.scan_tmp, &lane.sort_tmp, &lane.labels_tmp, &lane.stage}) b->release();
+        for (int i = 0; i < 2; ++i) {
+            if (lane.pin[i]) cudaFreeHost(lane.pin[i]);
+            if (lane.pin_ev[i]) cudaEventDestroy(lane.pin_ev[i]);
+        }
+        for (auto& half : lane.stage_ev)
+            for (auto& ev : half)
+                if (ev) cudaEventDestroy(ev);
     }
     for (cudaEvent_t e : ctx->ev) cudaEventDestroy(e);
     if (ctx->pool) cudaMemPoolDestroy(ctx->pool);
     cudaStreamDestroy(ctx->stream);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     if (ctx->spread_stream) cudaStreamDestroy(ctx->spread_stream);
-    for (auto& zone : ctx->stage_ev)
-        for (auto& half : zone)
-            for (auto& ev : half)
-                if (ev) cudaEventDestroy(ev);
     delete ctx;
     return 0;
 }
@@ -1035,7 +1120,9 @@ int32_t twtml_num_features(const twtml_model* m, int64_t* d)
 }
 
 // ---- dense batches --------------------------------------------------------------------------
-static int32_t new_dense(twtml_ctx* ctx, int64_t n, int64_t d, twtml_batch** out)
+// defer_global: leave the multi-rank row-count exchange to the batch's first use (asynchronous ingest must not touch
+// the communicator, which belongs to the compute stream)
+static int32_t new_dense(twtml_ctx* ctx, int64_t n, int64_t d, twtml_batch** out, bool defer_global = false)
 {
     DenseCfg c;
     TW_TRY(dense_cfg(d, c));
@@ -1044,16 +1131,51 @@ static int32_t new_dense(twtml_ctx* ctx, int64_t n, int64_t d, twtml_batch** out
     b->n = n;
     b->d = d;
     b->ldx = (d + 2) & ~(int64_t)1;
+    b->rows_appended = n;
     make_plan(n, ctx->spr, c.R, b->plan);
     if (n > 0) {
         int rc0 = pool_alloc(ctx, reinterpret_cast<void**>(&b->X), sizeof(double) * (size_t)n * (size_t)b->ldx);
         if (rc0) { delete b; return rc0; }
     }
-    int rc = ctx_global_rows(ctx, n, &b->n_global, &b->row0_global);
-    if (rc) { pool_free(ctx, b->X); delete b; return rc; }
+    if (defer_global && ctx->world > 1) {
+        b->global_deferred = true;
+    } else {
+        int rc = ctx_global_rows(ctx, n, &b->n_global, &b->row0_global);
+        if (rc) { pool_free(ctx, b->X); delete b; return rc; }
+    }
     ctx->live_handles += 1;
     *out = b;
     return 0;
+}
+
+// rows [row0, row0 + nrows) of a dense batch from host memory, on `lane` (enqueued; nothing waits here)
+static int dense_rows_in(twtml_ctx* ctx, IngestLane& lane, twtml_batch* b, int64_t row0, int64_t nrows, const double* X, int64_t ld_x,
+                         const double* labels, double* labels_dev)
+{
+    const int64_t d = b->d, ldx = b->ldx;
+    if (page_locked(X)) { // page-locked caller memory: DMA straight from it, labels dropped in on the device
+        TW_TRY(upload_plain(ctx, lane, labels_dev, labels, sizeof(double) * (size_t)nrows));
+        if (ld_x == d) { // packed rows: flat copies + a device kernel to the row pitch
+            cudaError_t e = flat_dense_ingest(ctx, lane, b, row0, nrows, X, labels_dev);
+            if (e != cudaSuccess) return fail(e == cudaErrorMemoryAllocation ? TWTML_E_OOM : TWTML_E_CUDA, "dense ingest: %s", cudaGetErrorString(e));
+        } else {
+            TW_CUDA(cudaMemcpy2DAsync(b->X + row0 * ldx, (size_t)ldx * 8, X, (size_t)ld_x * 8, (size_t)d * 8, (size_t)nrows, cudaMemcpyHostToDevice, lane.stream));
+            k_scatter_labels<<<(unsigned)((nrows + 255) / 256), 256, 0, lane.stream>>>(b->X + row0 * ldx, ldx, (int)d, labels_dev, nrows);
+            TW_CUDA(cudaGetLastError());
+        }
+        return 0;
+    }
+    // pageable: pack rows [x.., label, pad] into the pinned ring, chunk k+1 while chunk k copies
+    return staged_upload(lane, b->X + row0 * ldx, (size_t)ldx * 8, nrows, [&](char* dst, int64_t r0, int64_t nr) {
+        parallel_rows(nr, 2048, [&](int64_t lo, int64_t hi) {
+            for (int64_t r = lo; r < hi; ++r) {
+                double* row = reinterpret_cast<double*>(dst) + r * ldx;
+                memcpy(row, X + (r0 + r) * ld_x, sizeof(double) * (size_t)d);
+                row[d] = labels[r0 + r];
+                for (int64_t j = d + 1; j < ldx; ++j) row[j] = 0.0;
+            }
+        });
+    });
 }
 
 int32_t twtml_batch_from_dense(twtml_ctx* ctx, int64_t n, int64_t d, const double* X, int64_t ld_x, const double* labels, twtml_batch** out)
@@ -1064,37 +1186,9 @@ int32_t twtml_batch_from_dense(twtml_ctx* ctx, int64_t n, int64_t d, const doubl
     twtml_batch* b = nullptr;
     TW_TRY(new_dense(ctx, n, d, &b));
     if (n > 0) {
-        const int64_t ldx = b->ldx;
-        cudaPointerAttributes pa{};
-        const bool pinned = cudaPointerGetAttributes(&pa, X) == cudaSuccess && pa.type == cudaMemoryTypeHost;
-        cudaGetLastError();
-        int rc = 0;
-        if (pinned) { // page-locked caller memory: strided DMA straight from it, labels scattered on the device
-            rc = ctx->tmp_a.reserve(sizeof(double) * (size_t)n);
-            if (!rc) rc = upload_plain(ctx, ctx->tmp_a.p, labels, sizeof(double) * (size_t)n);
-            if (!rc && ld_x == d) { // packed rows: flat copies + a device kernel to the row pitch
-                cudaError_t e = flat_dense_ingest(ctx, 0, ctx->stream, b, X, ctx->tmp_a.as<double>());
-                if (e != cudaSuccess) rc = fail(e == cudaErrorMemoryAllocation ? TWTML_E_OOM : TWTML_E_CUDA, "dense ingest: %s", cudaGetErrorString(e));
-            } else if (!rc) {
-                cudaError_t e = cudaMemcpy2DAsync(b->X, (size_t)ldx * 8, X, (size_t)ld_x * 8, (size_t)d * 8, (size_t)n, cudaMemcpyHostToDevice, ctx->stream);
-                if (e != cudaSuccess) rc = fail(TWTML_E_CUDA, "cudaMemcpy2DAsync: %s", cudaGetErrorString(e));
-                if (!rc) {
-                    k_scatter_labels<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(b->X, ldx, (int)d, ctx->tmp_a.as<double>(), n);
-                    if (cudaGetLastError() != cudaSuccess) rc = fail(TWTML_E_CUDA, "k_scatter_labels launch failed");
-                }
-            }
-        } else { // pageable: pack rows [x.., label, pad] into the pinned ring, chunk k+1 while chunk k copies
-            rc = staged_upload(ctx, b->X, (size_t)ldx * 8, n, [&](char* dst, int64_t r0, int64_t nr) {
-                parallel_rows(nr, 2048, [&](int64_t lo, int64_t hi) {
-                    for (int64_t r = lo; r < hi; ++r) {
-                        double* row = reinterpret_cast<double*>(dst) + r * ldx;
-                        memcpy(row, X + (r0 + r) * ld_x, sizeof(double) * (size_t)d);
-                        row[d] = labels[r0 + r];
-                        for (int64_t j = d + 1; j < ldx; ++j) row[j] = 0.0;
-                    }
-                });
-            });
-        }
+        IngestLane& lane = ctx->lane[0];
+        int rc = lane.labels_tmp.reserve(sizeof(double) * (size_t)n);
+        if (!rc) rc = dense_rows_in(ctx, lane, b, 0, n, X, ld_x, labels, lane.labels_tmp.as<double>());
         if (!rc && cudaStreamSynchronize(ctx->stream) != cudaSuccess) rc = fail(TWTML_E_CUDA, "upload failed: %s", cudaGetErrorString(cudaGetLastError()));
         if (rc) { pool_free(ctx, b->X); ctx->live_handles -= 1; delete b; return rc; }
     }
@@ -1102,34 +1196,19 @@ int32_t twtml_batch_from_dense(twtml_ctx* ctx, int64_t n, int64_t d, const doubl
     return 0;
 }
 
-int32_t twtml_batch_from_dense_async(twtml_ctx* ctx, int64_t n, int64_t d, const double* X, int64_t ld_x, const double* labels, twtml_batch** out)
+// A dense batch whose memory is reserved now and whose rows arrive later, on the copy stream.
+static int32_t begin_dense_async(twtml_ctx* ctx, int64_t n, int64_t d, twtml_batch** out)
 {
-    if (!ctx || !out) return fail(TWTML_E_INVALID_ARG, "null argument");
-    if (n < 0 || d < 1 || (n > 0 && (!X || !labels)) || ld_x < d) return fail(TWTML_E_INVALID_ARG, "twtml_batch_from_dense_async: bad shape or null data");
-    // only page-locked host memory can be copied without a host-side staging pass, and the row-count
-    // exchange of a multi-rank context would have to wait for the compute stream: both fall back
-    if (n == 0 || ctx->world != 1 || !page_locked(X) || !page_locked(labels)) return twtml_batch_from_dense(ctx, n, d, X, ld_x, labels, out);
-    Guard g(ctx);
     twtml_batch* b = nullptr;
-    TW_TRY(new_dense(ctx, n, d, &b));
-    if (int rc = pool_alloc(ctx, reinterpret_cast<void**>(&b->labels), sizeof(double) * (size_t)n)) { batch_free_locked(b); return rc; }
+    TW_TRY(new_dense(ctx, n, d, &b, true));
+    b->rows_appended = 0;
+    if (int rc = pool_alloc(ctx, reinterpret_cast<void**>(&b->labels), sizeof(double) * (size_t)std::max<int64_t>(n, 1))) { batch_free_locked(b); return rc; }
     cudaError_t e = cudaEventCreateWithFlags(&b->ready, cudaEventDisableTiming);
     // the two buffers were allocated in compute-stream order: the copy stream may touch them only after that point
     if (e == cudaSuccess) e = cudaEventRecord(b->ready, ctx->stream);
     if (e == cudaSuccess) e = cudaStreamWaitEvent(ctx->copy_stream, b->ready, 0);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(b->labels, labels, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, ctx->copy_stream);
-    if (e == cudaSuccess && ld_x == d) {
-        e = flat_dense_ingest(ctx, 1, ctx->copy_stream, b, X, b->labels);
-    } else if (e == cudaSuccess) {
-        e = cudaMemcpy2DAsync(b->X, (size_t)b->ldx * 8, X, (size_t)ld_x * 8, (size_t)d * 8, (size_t)n, cudaMemcpyHostToDevice, ctx->copy_stream);
-        if (e == cudaSuccess) {
-            k_scatter_labels<<<(unsigned)((n + 255) / 256), 256, 0, ctx->copy_stream>>>(b->X, b->ldx, (int)d, b->labels, n);
-            e = cudaGetLastError();
-        }
-    }
-    if (e == cudaSuccess) e = cudaEventRecord(b->ready, ctx->copy_stream);
     if (e != cudaSuccess) {
-        int rc = fail(e == cudaErrorMemoryAllocation ? TWTML_E_OOM : TWTML_E_CUDA, "asynchronous ingest: %s", cudaGetErrorString(e));
+        int rc = fail(TWTML_E_CUDA, "asynchronous ingest: %s", cudaGetErrorString(e));
         batch_free_locked(b);
         return rc;
     }
@@ -1137,10 +1216,64 @@ int32_t twtml_batch_from_dense_async(twtml_ctx* ctx, int64_t n, int64_t d, const
     return 0;
 }
 
+static int32_t append_dense_async(twtml_ctx* ctx, twtml_batch* b, int64_t row0, int64_t nrows, const double* X, int64_t ld_x, const double* labels)
+{
+    std::lock_guard<std::mutex> lane_lock(ctx->lane[1].mu);
+    TW_TRY(dense_rows_in(ctx, ctx->lane[1], b, row0, nrows, X, ld_x, labels, b->labels + row0));
+    TW_CUDA(cudaEventRecord(b->ready, ctx->copy_stream));
+    b->rows_appended += nrows;
+    return 0;
+}
+
+int32_t twtml_batch_from_dense_async(twtml_ctx* ctx, int64_t n, int64_t d, const double* X, int64_t ld_x, const double* labels, twtml_batch** out)
+{
+    if (!ctx || !out) return fail(TWTML_E_INVALID_ARG, "null argument");
+    if (n < 0 || d < 1 || (n > 0 && (!X || !labels)) || ld_x < d) return fail(TWTML_E_INVALID_ARG, "twtml_batch_from_dense_async: bad shape or null data");
+    // only page-locked host memory can be copied without a host-side staging pass
+    if (n > 0 && (!page_locked(X) || !page_locked(labels))) return twtml_batch_from_dense(ctx, n, d, X, ld_x, labels, out);
+    Guard g(ctx);
+    twtml_batch* b = nullptr;
+    TW_TRY(begin_dense_async(ctx, n, d, &b));
+    if (n > 0) {
+        if (int rc = append_dense_async(ctx, b, 0, n, X, ld_x, labels)) { batch_free_locked(b); return rc; }
+    }
+    *out = b;
+    return 0;
+}
+
+int32_t twtml_batch_dense_begin(twtml_ctx* ctx, int64_t n, int64_t d, twtml_batch** out)
+{
+    if (!ctx || !out) return fail(TWTML_E_INVALID_ARG, "null argument");
+    if (n < 0 || d < 1) return fail(TWTML_E_INVALID_ARG, "twtml_batch_dense_begin: bad shape");
+    Guard g(ctx);
+    return begin_dense_async(ctx, n, d, out);
+}
+
+int32_t twtml_batch_dense_append(twtml_batch* b, int64_t nrows, const double* X, int64_t ld_x, const double* labels)
+{
+    if (!b) return fail(TWTML_E_INVALID_ARG, "null batch");
+    if (b->csr || !b->ready) return fail(TWTML_E_INVALID_ARG, "twtml_batch_dense_append: not a batch from twtml_batch_dense_begin");
+    if (nrows < 0 || (nrows > 0 && (!X || !labels)) || ld_x < b->d) return fail(TWTML_E_INVALID_ARG, "twtml_batch_dense_append: bad shape or null data");
+    if (b->rows_appended + nrows > b->n)
+        return fail(TWTML_E_INVALID_ARG, "twtml_batch_dense_append: %lld rows after %lld exceed the batch's %lld", (long long)nrows, (long long)b->rows_appended, (long long)b->n);
+    if (nrows == 0) return 0;
+    twtml_ctx* ctx = b->ctx;
+    Guard g(ctx);
+    return append_dense_async(ctx, b, b->rows_appended, nrows, X, ld_x, labels);
+}
+
 int32_t twtml_batch_ready(const twtml_batch* b, int32_t wait, int32_t* ready)
 {
     if (!b) return fail(TWTML_E_INVALID_ARG, "null batch");
     int r = 1;
+    if (b->has_pending) { // asynchronous CSR / tweet ingest: the worker's verdict first
+        if (!wait && b->pending.wait_for(std::chrono::seconds(0)) != std::future_status::ready) {
+            if (ready) *ready = 0;
+            return 0;
+        }
+        const int rc = b->pending.get();
+        if (rc) return fail(rc, "asynchronous ingest failed: %s", b->pending_err.c_str());
+    }
     if (b->ready) {
         Guard g(b->ctx);
         if (wait) TW_CUDA(cudaEventSynchronize(b->ready));
@@ -1184,6 +1317,10 @@ int32_t twtml_batch_rows(const twtml_batch* b, int64_t* n)
 int32_t twtml_batch_info(const twtml_batch* b, int64_t* n, int64_t* d, int64_t* nnz, int32_t* is_csr)
 {
     if (!b) return fail(TWTML_E_INVALID_ARG, "null batch");
+    if (nnz && b->has_pending) { // only the finished ingest knows how many entries a featurised batch has
+        const int rc = b->pending.get();
+        if (rc) return fail(rc, "asynchronous ingest failed: %s", b->pending_err.c_str());
+    }
     if (n) *n = b->n;
     if (d) *d = b->d;
     if (nnz) *nnz = b->csr ? b->nnz : b->n * b->d;
@@ -1224,8 +1361,8 @@ int32_t twtml_predict(const twtml_model* m, const twtml_batch* b, double* out_pr
     if (!out_pred && b->n > 0) return fail(TWTML_E_INVALID_ARG, "twtml_predict: out_pred is null");
     twtml_ctx* ctx = m->ctx;
     Guard g(ctx);
-    if (b->n == 0) return 0;
     TW_TRY(wait_ready(ctx, b));
+    if (b->n == 0) return 0;
     TW_TRY(reserve_scratch(ctx, m, b));
     TW_TRY(ctx->tmp_a.reserve(sizeof(double) * (size_t)b->n));
     TW_TRY(run_pass(ctx, m, b, MODE_PREDICT, ctx->tmp_a.as<double>(), nullptr, 0));

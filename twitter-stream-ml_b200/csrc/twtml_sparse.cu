@@ -9,6 +9,7 @@
 #include <atomic>
 #include <cmath>
 #include <cstring>
+#include <mutex>
 #include <thread>
 #include <vector>
 
@@ -23,18 +24,18 @@
 namespace twtml {
 
 template <class T>
-static int dev_alloc(twtml_ctx* ctx, T** p, size_t count)
+static int dev_alloc(twtml_ctx* ctx, IngestLane& lane, T** p, size_t count)
 {
-    return pool_alloc(ctx, reinterpret_cast<void**>(p), sizeof(T) * std::max<size_t>(count, 1));
+    return pool_alloc(ctx, reinterpret_cast<void**>(p), sizeof(T) * std::max<size_t>(count, 1), lane.stream);
 }
 
-static int exclusive_sum(twtml_ctx* ctx, const long long* in, long long* out, long long n)
+static int exclusive_sum(IngestLane& lane, const long long* in, long long* out, long long n)
 {
     size_t tmp = 0;
     cudaGetLastError(); // CUB reports any error still pending in the runtime as its own
-    TW_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp, in, out, n, ctx->stream));
-    TW_TRY(ctx->gather.reserve(tmp));
-    TW_CUDA(cub::DeviceScan::ExclusiveSum(ctx->gather.p, tmp, in, out, n, ctx->stream));
+    TW_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp, in, out, n, lane.stream));
+    TW_TRY(lane.scan_tmp.reserve(tmp));
+    TW_CUDA(cub::DeviceScan::ExclusiveSum(lane.scan_tmp.p, tmp, in, out, n, lane.stream));
     return 0;
 }
 
@@ -42,7 +43,7 @@ static unsigned blocks_for(long long n, int threads) { return (unsigned)std::max
 
 // Narrow models: no transpose at all, only the first row of every CTA of the single-pass kernel.
 // Returns 1 when the batch does not qualify (the caller then builds the global transpose).
-static int csr_finalize_narrow(twtml_ctx* ctx, twtml_batch* b)
+static int csr_finalize_narrow(twtml_ctx* ctx, IngestLane& lane, twtml_batch* b)
 {
     const long long n = b->n;
     const int d = (int)b->d;
@@ -50,9 +51,9 @@ static int csr_finalize_narrow(twtml_ctx* ctx, twtml_batch* b)
     const int warps = narrow_warps(d);
     if (warps < 4) return 1;
     // one partial vector per CTA of a grid fixed here: the plan's "blocks" are those CTAs
-    const long long grid = std::max<long long>(1, std::min<long long>((n + warps - 1) / warps, (long long)ctx->sm_count));
-    TW_TRY(dev_alloc(ctx, &b->bounds, (size_t)grid + 1));
-    k_narrow_bounds<<<blocks_for(grid + 1, 256), 256, 0, ctx->stream>>>(b->rowptr, n, grid, b->bounds);
+    const long long grid = std::max<long long>(1, std::min<long long>((n + warps - 1) / warps, (long long)ctx->sm_count * narrow_ctas_per_sm(d)));
+    TW_TRY(dev_alloc(ctx, lane, &b->bounds, (size_t)grid + 1));
+    k_narrow_bounds<<<blocks_for(grid + 1, 256), 256, 0, lane.stream>>>(b->rowptr, n, grid, b->bounds);
     TW_CUDA(cudaGetLastError());
     b->narrow = true;
     b->nwarps = warps;
@@ -64,82 +65,80 @@ static int csr_finalize_narrow(twtml_ctx* ctx, twtml_batch* b)
     return 0;
 }
 
-// rowptr / colidx / vals / labels are on the device: build the plan, the transpose and the column tasks
-static int csr_finalize(twtml_ctx* ctx, twtml_batch* b)
+// rowptr / colidx / vals / labels are on the device (or on their way, in the lane's stream order): build the plan,
+// the transpose and the column tasks.  Everything is enqueued on the lane's stream; nothing here waits for the device.
+static int csr_finalize(twtml_ctx* ctx, IngestLane& lane, twtml_batch* b, bool defer_global)
 {
     // one shard per rank (the column sums are per rank, not per virtual shard); row blocks small enough to give every SM
     // several CTAs of the row pass even for a modest micro-batch (but at least 32 rows: one step of the widest row form)
     make_plan(b->n, 1, 32, b->plan, 4096);
-    TW_TRY(ctx_global_rows(ctx, b->n, &b->n_global, &b->row0_global));
+    if (defer_global && ctx->world > 1) b->global_deferred = true;
+    else TW_TRY(ctx_global_rows(ctx, b->n, &b->n_global, &b->row0_global));
     if (b->nnz >= ((long long)1 << 31) || b->n >= ((long long)1 << 31))
         return fail(TWTML_E_INVALID_ARG, "CSR batch too large for 32-bit entry indices (%lld rows, %lld nnz per GPU)", (long long)b->n, (long long)b->nnz);
     {
-        const int nrc = csr_finalize_narrow(ctx, b);
+        const int nrc = csr_finalize_narrow(ctx, lane, b);
         if (nrc <= 0) return nrc; // built (0) or failed (< 0); 1 = not a narrow batch
     }
+    cudaStream_t st = lane.stream;
     const int d = (int)b->d;
     const long long nnz = b->nnz;
     const long long nwin = (nnz + kWin - 1) / kWin;
     b->nwin = nwin;
-    TW_TRY(dev_alloc(ctx, &b->colptr, (size_t)d + 1));
-    TW_TRY(dev_alloc(ctx, &b->rowidx, (size_t)nnz));
-    TW_TRY(dev_alloc(ctx, &b->cvals, (size_t)nnz));
-    TW_TRY(dev_alloc(ctx, &b->diff, (size_t)b->n));
-    TW_TRY(dev_alloc(ctx, &b->headbits, (size_t)(nwin + 1) * 8));
-    TW_TRY(dev_alloc(ctx, &b->win_first_nz, (size_t)nwin + 1));
-    TW_TRY(dev_alloc(ctx, &b->wkey, (size_t)nwin + 1));
-    TW_TRY(dev_alloc(ctx, &b->win_first_part, (size_t)nwin + 1));
-    TW_TRY(dev_alloc(ctx, &b->win_last_part, (size_t)nwin + 1));
-    TW_TRY(dev_alloc(ctx, &b->nzcol, (size_t)std::min<long long>(nnz, d) + 1));
-    TW_CUDA(cudaMemsetAsync(b->headbits, 0, sizeof(unsigned) * (size_t)(nwin + 1) * 8, ctx->stream));
+    TW_TRY(dev_alloc(ctx, lane, &b->colptr, (size_t)d + 1));
+    TW_TRY(dev_alloc(ctx, lane, &b->rowidx, (size_t)nnz));
+    TW_TRY(dev_alloc(ctx, lane, &b->cvals, (size_t)nnz));
+    TW_TRY(dev_alloc(ctx, lane, &b->diff, (size_t)b->n));
+    TW_TRY(dev_alloc(ctx, lane, &b->headbits, (size_t)(nwin + 1) * 8));
+    TW_TRY(dev_alloc(ctx, lane, &b->win_first_nz, (size_t)nwin + 1));
+    TW_TRY(dev_alloc(ctx, lane, &b->wkey, (size_t)nwin + 1));
+    TW_TRY(dev_alloc(ctx, lane, &b->win_first_part, (size_t)nwin + 1));
+    TW_TRY(dev_alloc(ctx, lane, &b->win_last_part, (size_t)nwin + 1));
+    TW_TRY(dev_alloc(ctx, lane, &b->nzcol, (size_t)std::min<long long>(nnz, d) + 1));
+    TW_CUDA(cudaMemsetAsync(b->headbits, 0, sizeof(unsigned) * (size_t)(nwin + 1) * 8, st));
     if (nnz > 0) {
         int *keys_out = nullptr, *iota = nullptr, *perm = nullptr;
-        TW_TRY(dev_alloc(ctx, &keys_out, (size_t)nnz));
-        TW_TRY(dev_alloc(ctx, &iota, (size_t)nnz));
-        TW_TRY(dev_alloc(ctx, &perm, (size_t)nnz));
-        int rc = 0;
+        long long* winheads = nullptr;
+        int rc = dev_alloc(ctx, lane, &keys_out, (size_t)nnz);
+        if (!rc) rc = dev_alloc(ctx, lane, &iota, (size_t)nnz);
+        if (!rc) rc = dev_alloc(ctx, lane, &perm, (size_t)nnz);
+        if (!rc) rc = dev_alloc(ctx, lane, &winheads, (size_t)nwin + 1);
         do {
-            k_iota<<<blocks_for(nnz, 256), 256, 0, ctx->stream>>>(iota, nnz);
+            if (rc) break;
+            k_iota<<<blocks_for(nnz, 256), 256, 0, st>>>(iota, nnz);
             int bits = 1;
             while (((long long)1 << bits) < d) ++bits;
             size_t tmp = 0;
             cudaGetLastError();
-            cudaError_t e = cub::DeviceRadixSort::SortPairs(nullptr, tmp, b->colidx, keys_out, iota, perm, (int)nnz, 0, bits, ctx->stream);
+            cudaError_t e = cub::DeviceRadixSort::SortPairs(nullptr, tmp, b->colidx, keys_out, iota, perm, (int)nnz, 0, bits, st);
             if (e != cudaSuccess) { rc = fail(TWTML_E_CUDA, "radix sort sizing: %s", cudaGetErrorString(e)); break; }
-            if ((rc = ctx->tmp_a.reserve(tmp))) break;
+            if ((rc = lane.sort_tmp.reserve(tmp))) break;
             // LSD radix sort is stable: entries of a column keep their CSR (row) order
-            e = cub::DeviceRadixSort::SortPairs(ctx->tmp_a.p, tmp, b->colidx, keys_out, iota, perm, (int)nnz, 0, bits, ctx->stream);
+            e = cub::DeviceRadixSort::SortPairs(lane.sort_tmp.p, tmp, b->colidx, keys_out, iota, perm, (int)nnz, 0, bits, st);
             if (e != cudaSuccess) { rc = fail(TWTML_E_CUDA, "radix sort: %s", cudaGetErrorString(e)); break; }
-            k_colptr<<<blocks_for(nnz + 1, 256), 256, 0, ctx->stream>>>(keys_out, nnz, d, b->colptr);
-            k_csc_gather<<<blocks_for(nnz, 256), 256, 0, ctx->stream>>>(perm, b->rowptr, b->n, b->vals, nnz, b->rowidx, b->cvals);
+            k_colptr<<<blocks_for(nnz + 1, 256), 256, 0, st>>>(keys_out, nnz, d, b->colptr);
+            k_csc_gather<<<blocks_for(nnz, 256), 256, 0, st>>>(perm, b->rowptr, b->n, b->vals, nnz, b->rowidx, b->cvals);
             // window index of the transpose: head bits, heads per window -> first non-empty column per window
-            k_csc_headbits<<<blocks_for(nnz + 1, 256), 256, 0, ctx->stream>>>(keys_out, nnz, b->headbits);
-            long long* winheads = reinterpret_cast<long long*>(iota); // iota is dead from here on; nnz ints >= nwin+1 int64 when nnz >= 2
-            long long* winheads_own = nullptr;
-            if ((size_t)nnz * sizeof(int) < (size_t)(nwin + 1) * sizeof(long long)) {
-                if ((rc = dev_alloc(ctx, &winheads_own, (size_t)nwin + 1))) break;
-                winheads = winheads_own;
-            }
-            k_csc_winmeta<<<blocks_for(nwin + 1, 256), 256, 0, ctx->stream>>>(b->headbits, keys_out, nnz, nwin, winheads, b->wkey);
-            rc = exclusive_sum(ctx, winheads, b->win_first_nz, nwin + 1);
-            if (!rc) k_csc_nzcol<<<blocks_for(nnz, 256), 256, 0, ctx->stream>>>(keys_out, b->headbits, b->win_first_nz, nnz, b->nzcol);
+            k_csc_headbits<<<blocks_for(nnz + 1, 256), 256, 0, st>>>(keys_out, nnz, b->headbits);
+            k_csc_winmeta<<<blocks_for(nwin + 1, 256), 256, 0, st>>>(b->headbits, keys_out, nnz, nwin, winheads, b->wkey);
+            rc = exclusive_sum(lane, winheads, b->win_first_nz, nwin + 1);
+            if (!rc) k_csc_nzcol<<<blocks_for(nnz, 256), 256, 0, st>>>(keys_out, b->headbits, b->win_first_nz, nnz, b->nzcol);
             if (!rc && cudaGetLastError() != cudaSuccess) rc = fail(TWTML_E_CUDA, "transpose kernels failed to launch");
-            cudaStreamSynchronize(ctx->stream);
-            pool_free(ctx, winheads_own);
         } while (0);
-        cudaStreamSynchronize(ctx->stream);
-        pool_free(ctx, keys_out);
-        pool_free(ctx, iota);
-        pool_free(ctx, perm);
+        // stream-ordered frees: the temporaries go back to the pool once the kernels above are done with them
+        pool_free(ctx, winheads, st);
+        pool_free(ctx, keys_out, st);
+        pool_free(ctx, iota, st);
+        pool_free(ctx, perm, st);
         if (rc) return rc;
     } else {
-        TW_CUDA(cudaMemsetAsync(b->colptr, 0, sizeof(long long) * ((size_t)d + 1), ctx->stream));
-        TW_CUDA(cudaStreamSynchronize(ctx->stream));
+        TW_CUDA(cudaMemsetAsync(b->colptr, 0, sizeof(long long) * ((size_t)d + 1), st));
     }
     return 0;
 }
 
-static int new_csr(twtml_ctx* ctx, int64_t n, int64_t d, int64_t nnz, twtml_batch** out)
+// the handle alone: what an asynchronous ingest hands back at once
+static twtml_batch* csr_shell(twtml_ctx* ctx, int64_t n, int64_t d, int64_t nnz)
 {
     twtml_batch* b = new twtml_batch();
     b->ctx = ctx;
@@ -147,12 +146,24 @@ static int new_csr(twtml_ctx* ctx, int64_t n, int64_t d, int64_t nnz, twtml_batc
     b->n = n;
     b->d = d;
     b->nnz = nnz;
-    ctx->live_handles += 1; // released by twtml_batch_free, also on the failure paths below and in the callers
+    ctx->live_handles += 1; // released by twtml_batch_free, also on the failure paths of the callers
+    return b;
+}
+
+static int csr_alloc(twtml_ctx* ctx, IngestLane& lane, twtml_batch* b)
+{
     // colidx / vals end in kNarrowSlack spare entries: the narrow kernel's bulk copies are 16 bytes wide
-    int rc = dev_alloc(ctx, &b->rowptr, (size_t)n + 1);
-    if (!rc) rc = dev_alloc(ctx, &b->colidx, (size_t)nnz + kNarrowSlack);
-    if (!rc) rc = dev_alloc(ctx, &b->vals, (size_t)nnz + kNarrowSlack);
-    if (!rc) rc = dev_alloc(ctx, &b->labels, (size_t)n);
+    TW_TRY(dev_alloc(ctx, lane, &b->rowptr, (size_t)b->n + 1));
+    TW_TRY(dev_alloc(ctx, lane, &b->colidx, (size_t)b->nnz + kNarrowSlack));
+    TW_TRY(dev_alloc(ctx, lane, &b->vals, (size_t)b->nnz + kNarrowSlack));
+    TW_TRY(dev_alloc(ctx, lane, &b->labels, (size_t)b->n));
+    return 0;
+}
+
+static int new_csr(twtml_ctx* ctx, IngestLane& lane, int64_t n, int64_t d, int64_t nnz, twtml_batch** out)
+{
+    twtml_batch* b = csr_shell(ctx, n, d, nnz);
+    int rc = csr_alloc(ctx, lane, b);
     if (rc) { batch_free_locked(b); return rc; }
     *out = b;
     return 0;
@@ -269,15 +280,188 @@ int csr_reduce(twtml_ctx* ctx, const twtml_batch* b, double* shard_out, const Tr
 
 static int lower_table(twtml_ctx* ctx, const uint16_t** out)
 {
+    static std::mutex mu; // first use may come from the caller's thread or from the ingest worker
+    std::lock_guard<std::mutex> lk(mu);
     if (!ctx->lower.p) {
         std::vector<uint16_t> t(65536);
         for (int c = 0; c < 65536; ++c) t[c] = (uint16_t)c;
         for (int i = 0; i < kLowerPairCount; ++i) t[kLowerPairs[i][0]] = kLowerPairs[i][1];
-        TW_TRY(ctx->lower.reserve(sizeof(uint16_t) * 65536));
-        TW_CUDA(cudaMemcpyAsync(ctx->lower.p, t.data(), sizeof(uint16_t) * 65536, cudaMemcpyHostToDevice, ctx->stream));
-        TW_CUDA(cudaStreamSynchronize(ctx->stream));
+        DevBuf buf;
+        TW_TRY(buf.reserve(sizeof(uint16_t) * 65536));
+        cudaError_t e = cudaMemcpy(buf.p, t.data(), sizeof(uint16_t) * 65536, cudaMemcpyHostToDevice); // blocking: the table is complete before anyone sees the pointer
+        if (e != cudaSuccess) { buf.release(); return fail(TWTML_E_CUDA, "lower-case table: %s", cudaGetErrorString(e)); }
+        ctx->lower = buf;
     }
     *out = ctx->lower.as<uint16_t>();
+    return 0;
+}
+
+// ---- ingest bodies: the same code serves the blocking calls (lane 0, caller's thread) and the asynchronous ones
+// (lane 1, the context's worker thread) ----------------------------------------------------------------------
+
+// Vectors.sparse require()s strictly increasing, in-range indices [U]
+static int validate_csr(int64_t n, int64_t d, int64_t nnz, const int64_t* rowptr, const int32_t* colidx)
+{
+    // the row pointers alone first (a malformed one must be refused before any index is read through it)
+    for (int64_t r = 0; r < n; ++r)
+        if (rowptr[r] < 0 || rowptr[r] > rowptr[r + 1] || rowptr[r + 1] > nnz)
+            return fail(TWTML_E_INVALID_ARG, "row %lld: rowptr must be non-decreasing within [0, rowptr[n]]", (long long)r);
+    std::atomic<int64_t> bad_row(-1);
+    const unsigned hw = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+    const int nt = (int)std::min<int64_t>(hw, std::max<int64_t>(1, n / 4096));
+    auto scan = [&](int64_t lo, int64_t hi) { // on all host threads
+        for (int64_t r = lo; r < hi && bad_row.load(std::memory_order_relaxed) < 0; ++r) {
+            bool ok = true;
+            for (int64_t k = rowptr[r]; ok && k < rowptr[r + 1]; ++k)
+                ok = colidx[k] >= 0 && colidx[k] < d && (k == rowptr[r] || colidx[k] > colidx[k - 1]);
+            if (!ok) bad_row.store(r);
+        }
+    };
+    if (nt <= 1) scan(0, n);
+    else {
+        std::vector<std::thread> th;
+        for (int i = 0; i < nt; ++i) th.emplace_back(scan, n * i / nt, n * (i + 1) / nt);
+        for (auto& t : th) t.join();
+    }
+    if (bad_row.load() >= 0)
+        return fail(TWTML_E_INVALID_ARG, "row %lld: indices must be strictly increasing and < %lld", (long long)bad_row.load(), (long long)d);
+    return 0;
+}
+
+static int csr_ingest(twtml_ctx* ctx, IngestLane& lane, twtml_batch* b, const int64_t* rowptr, const int32_t* colidx, const double* vals,
+                      const double* labels, bool defer_global)
+{
+    std::lock_guard<std::mutex> lane_lock(lane.mu);
+    const int64_t n = b->n, nnz = b->nnz;
+    TW_TRY(validate_csr(n, b->d, nnz, rowptr, colidx));
+    TW_TRY(csr_alloc(ctx, lane, b));
+    TW_TRY(upload_plain(ctx, lane, b->rowptr, rowptr, sizeof(int64_t) * (size_t)(n + 1)));
+    if (nnz) TW_TRY(upload_plain(ctx, lane, b->colidx, colidx, sizeof(int32_t) * (size_t)nnz));
+    if (nnz) TW_TRY(upload_plain(ctx, lane, b->vals, vals, sizeof(double) * (size_t)nnz));
+    if (n) TW_TRY(upload_plain(ctx, lane, b->labels, labels, sizeof(double) * (size_t)n));
+    TW_TRY(csr_finalize(ctx, lane, b, defer_global));
+    if (b->ready) TW_CUDA(cudaEventRecord(b->ready, lane.stream));
+    return 0;
+}
+
+struct TweetArgs {
+    const uint16_t* text_utf16;
+    const int64_t* text_off;
+    const int32_t *retweet_cnt, *followers, *favourites, *friends;
+    const int64_t* created_ms;
+    const uint8_t* is_retweet;
+    int64_t n, now_ms;
+    int32_t rt_begin, rt_end, F;
+    uint32_t flags;
+};
+
+// rows that pass MllibHelper.filtrate (:89-94): the host can tell without the GPU, so an asynchronously ingested batch
+// knows its row count (rdd.count, LinearRegression.scala:59) at once; also refuses texts the featuriser cannot hold
+static int tweets_precheck(const TweetArgs& t, int64_t* n_kept)
+{
+    int64_t kept = 0;
+    for (int64_t i = 0; i < t.n; ++i) {
+        const int64_t len = t.text_off[i + 1] - t.text_off[i];
+        if (len < 0) return fail(TWTML_E_INVALID_ARG, "twtml_batch_from_tweets: text offsets decrease at tweet %lld", (long long)i);
+        if (len > kMaxTerms + 1) return fail(TWTML_E_INVALID_ARG, "a tweet has %lld UTF-16 units; the featuriser takes at most %d", (long long)len, kMaxTerms + 1);
+        kept += t.is_retweet[i] != 0 && t.retweet_cnt[i] >= t.rt_begin && t.retweet_cnt[i] <= t.rt_end;
+    }
+    *n_kept = kept;
+    return 0;
+}
+
+static int tweets_ingest(twtml_ctx* ctx, IngestLane& lane, twtml_batch* b, const TweetArgs& t, bool defer_global)
+{
+    std::lock_guard<std::mutex> lane_lock(lane.mu);
+    cudaStream_t st = lane.stream;
+    const int64_t n = t.n;
+    const int F = t.F;
+    if (n == 0) {
+        TW_TRY(csr_alloc(ctx, lane, b));
+        TW_CUDA(cudaMemsetAsync(b->rowptr, 0, sizeof(long long), st));
+        TW_TRY(csr_finalize(ctx, lane, b, defer_global));
+        if (b->ready) TW_CUDA(cudaEventRecord(b->ready, st));
+        return 0;
+    }
+    const int64_t units = t.text_off[n];
+    // device copies of the tweet columns
+    uint16_t* d_text = nullptr;
+    long long *d_off = nullptr, *d_created = nullptr, *keep = nullptr, *rownnz = nullptr, *krow = nullptr, *eoff = nullptr;
+    int *d_rc = nullptr, *d_fo = nullptr, *d_fa = nullptr, *d_fr = nullptr, *pair_idx = nullptr, *pair_cnt = nullptr;
+    uint8_t* d_rt = nullptr;
+    std::vector<void*> owned;
+    auto cleanup = [&]() { for (void* p : owned) pool_free(ctx, p, st); };
+#define TW_OWN(call, ptrvar) do { int rc_ = (call); if (rc_) { cleanup(); return rc_; } owned.push_back(ptrvar); } while (0)
+#define TW_DO(call) do { int rc_ = (call); if (rc_) { cleanup(); return rc_; } } while (0)
+    TW_OWN(dev_alloc(ctx, lane, &d_text, (size_t)units), d_text);
+    TW_OWN(dev_alloc(ctx, lane, &d_off, (size_t)n + 1), d_off);
+    TW_OWN(dev_alloc(ctx, lane, &d_created, (size_t)n), d_created);
+    TW_OWN(dev_alloc(ctx, lane, &d_rc, (size_t)n), d_rc);
+    TW_OWN(dev_alloc(ctx, lane, &d_fo, (size_t)n), d_fo);
+    TW_OWN(dev_alloc(ctx, lane, &d_fa, (size_t)n), d_fa);
+    TW_OWN(dev_alloc(ctx, lane, &d_fr, (size_t)n), d_fr);
+    TW_OWN(dev_alloc(ctx, lane, &d_rt, (size_t)n), d_rt);
+    TW_OWN(dev_alloc(ctx, lane, &pair_idx, (size_t)units), pair_idx);
+    TW_OWN(dev_alloc(ctx, lane, &pair_cnt, (size_t)units), pair_cnt);
+    TW_OWN(dev_alloc(ctx, lane, &keep, (size_t)n + 1), keep);
+    TW_OWN(dev_alloc(ctx, lane, &rownnz, (size_t)n + 1), rownnz);
+    TW_OWN(dev_alloc(ctx, lane, &krow, (size_t)n + 1), krow);
+    TW_OWN(dev_alloc(ctx, lane, &eoff, (size_t)n + 1), eoff);
+    if (units) TW_DO(upload_plain(ctx, lane, d_text, t.text_utf16, sizeof(uint16_t) * (size_t)units));
+    TW_DO(upload_plain(ctx, lane, d_off, t.text_off, sizeof(int64_t) * (size_t)(n + 1)));
+    TW_DO(upload_plain(ctx, lane, d_created, t.created_ms, sizeof(int64_t) * (size_t)n));
+    TW_DO(upload_plain(ctx, lane, d_rc, t.retweet_cnt, sizeof(int32_t) * (size_t)n));
+    TW_DO(upload_plain(ctx, lane, d_fo, t.followers, sizeof(int32_t) * (size_t)n));
+    TW_DO(upload_plain(ctx, lane, d_fa, t.favourites, sizeof(int32_t) * (size_t)n));
+    TW_DO(upload_plain(ctx, lane, d_fr, t.friends, sizeof(int32_t) * (size_t)n));
+    TW_DO(upload_plain(ctx, lane, d_rt, t.is_retweet, (size_t)n));
+
+    const uint16_t* lower = nullptr;
+    if (t.flags & TWTML_FLAG_LOWERCASE) TW_DO(lower_table(ctx, &lower));
+    TweetCols tc{d_text, d_off, d_rc, d_fo, d_fa, d_fr, d_created, d_rt};
+    cudaMemsetAsync(keep + n, 0, sizeof(long long), st);
+    cudaMemsetAsync(rownnz + n, 0, sizeof(long long), st);
+    const unsigned gridA = (unsigned)std::min<long long>((n + kFeatWarps - 1) / kFeatWarps, (long long)ctx->sm_count * 16);
+    k_feat_terms<<<gridA, kFeatWarps * 32, 0, st>>>(tc, n, t.rt_begin, t.rt_end, F, lower, pair_idx, pair_cnt, keep, rownnz);
+    TW_DO(exclusive_sum(lane, keep, krow, n + 1));
+    TW_DO(exclusive_sum(lane, rownnz, eoff, n + 1));
+    // the one size only the device knows: how many entries the kept rows have (the row count was settled on the host)
+    long long tot[2] = {0, 0};
+    cudaMemcpyAsync(&tot[0], krow + n, sizeof(long long), cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(&tot[1], eoff + n, sizeof(long long), cudaMemcpyDeviceToHost, st);
+    if (cudaStreamSynchronize(st) != cudaSuccess) { cleanup(); return fail(TWTML_E_CUDA, "featuriser failed: %s", cudaGetErrorString(cudaGetLastError())); }
+    if (tot[0] != b->n) { cleanup(); return fail(TWTML_E_CUDA, "featuriser kept %lld rows, the host filter %lld", tot[0], (long long)b->n); }
+    b->nnz = tot[1];
+    TW_DO(csr_alloc(ctx, lane, b));
+    const unsigned gridB = (unsigned)std::min<long long>((n + 3) / 4, (long long)ctx->sm_count * 16);
+    k_feat_pack<<<gridB, 128, 0, st>>>(tc, n, t.now_ms, F, pair_idx, pair_cnt, keep, krow, rownnz, eoff, b->rowptr, b->colidx, b->vals, b->labels);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(b->rowptr + b->n, eoff + n, sizeof(long long), cudaMemcpyDeviceToDevice, st);
+    cleanup();
+#undef TW_OWN
+#undef TW_DO
+    if (e != cudaSuccess) return fail(TWTML_E_CUDA, "featuriser pack failed: %s", cudaGetErrorString(e));
+    TW_TRY(csr_finalize(ctx, lane, b, defer_global));
+    if (b->ready) TW_CUDA(cudaEventRecord(b->ready, st));
+    return 0;
+}
+
+static int check_tweet_args(twtml_ctx* ctx, twtml_batch** out, const TweetArgs& t)
+{
+    if (!ctx || !out) return fail(TWTML_E_INVALID_ARG, "null argument");
+    if (t.n < 0 || t.F < 1 || t.F > (1 << 30) - 4) return fail(TWTML_E_INVALID_ARG, "twtml_batch_from_tweets: bad sizes");
+    if (t.n > 0 && (!t.text_off || !t.retweet_cnt || !t.followers || !t.favourites || !t.friends || !t.created_ms || !t.is_retweet))
+        return fail(TWTML_E_INVALID_ARG, "twtml_batch_from_tweets: null column");
+    const int64_t units = t.n > 0 ? t.text_off[t.n] : 0;
+    if (t.n > 0 && (t.text_off[0] != 0 || units < 0 || (units > 0 && !t.text_utf16))) return fail(TWTML_E_INVALID_ARG, "twtml_batch_from_tweets: bad text offsets");
+    return 0;
+}
+
+// an event for a batch that is filled on the copy stream; batch memory is pool memory, so no ordering against the
+// compute stream is needed before the first touch (nothing of it existed before)
+static int make_ready_event(twtml_batch* b)
+{
+    TW_CUDA(cudaEventCreateWithFlags(&b->ready, cudaEventDisableTiming));
     return 0;
 }
 
@@ -287,47 +471,39 @@ using namespace twtml;
 
 extern "C" {
 
-int32_t twtml_batch_from_csr(twtml_ctx* ctx, int64_t n, int64_t d, const int64_t* rowptr, const int32_t* colidx, const double* vals,
-                             const double* labels, twtml_batch** out)
+static int32_t check_csr_args(twtml_ctx* ctx, int64_t n, int64_t d, const int64_t* rowptr, const int32_t* colidx, const double* vals,
+                              const double* labels, twtml_batch** out, int64_t* nnz_out)
 {
     if (!ctx || !out) return fail(TWTML_E_INVALID_ARG, "null argument");
     if (n < 0 || d < 1 || d > ((int64_t)1 << 30) || !rowptr || (n > 0 && !labels)) return fail(TWTML_E_INVALID_ARG, "twtml_batch_from_csr: bad shape or null data");
     const int64_t nnz = rowptr[n] - rowptr[0];
     if (rowptr[0] != 0 || nnz < 0 || (nnz > 0 && (!colidx || !vals))) return fail(TWTML_E_INVALID_ARG, "twtml_batch_from_csr: rowptr must start at 0 and be non-decreasing");
-    // the row pointers alone first (a malformed one must be refused before any index is read through it)
-    for (int64_t r = 0; r < n; ++r)
-        if (rowptr[r] < 0 || rowptr[r] > rowptr[r + 1] || rowptr[r + 1] > nnz)
-            return fail(TWTML_E_INVALID_ARG, "row %lld: rowptr must be non-decreasing within [0, rowptr[n]]", (long long)r);
-    { // Vectors.sparse require()s strictly increasing, in-range indices [U]; checked on all host threads
-        std::atomic<int64_t> bad_row(-1);
-        const unsigned hw = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
-        const int nt = (int)std::min<int64_t>(hw, std::max<int64_t>(1, n / 4096));
-        auto scan = [&](int64_t lo, int64_t hi) {
-            for (int64_t r = lo; r < hi && bad_row.load(std::memory_order_relaxed) < 0; ++r) {
-                bool ok = true;
-                for (int64_t k = rowptr[r]; ok && k < rowptr[r + 1]; ++k)
-                    ok = colidx[k] >= 0 && colidx[k] < d && (k == rowptr[r] || colidx[k] > colidx[k - 1]);
-                if (!ok) bad_row.store(r);
-            }
-        };
-        if (nt <= 1) scan(0, n);
-        else {
-            std::vector<std::thread> th;
-            for (int i = 0; i < nt; ++i) th.emplace_back(scan, n * i / nt, n * (i + 1) / nt);
-            for (auto& t : th) t.join();
-        }
-        if (bad_row.load() >= 0)
-            return fail(TWTML_E_INVALID_ARG, "row %lld: indices must be strictly increasing and < %lld", (long long)bad_row.load(), (long long)d);
-    }
+    *nnz_out = nnz;
+    return 0;
+}
+
+int32_t twtml_batch_from_csr(twtml_ctx* ctx, int64_t n, int64_t d, const int64_t* rowptr, const int32_t* colidx, const double* vals,
+                             const double* labels, twtml_batch** out)
+{
+    int64_t nnz = 0;
+    TW_TRY(check_csr_args(ctx, n, d, rowptr, colidx, vals, labels, out, &nnz));
     Guard g(ctx);
-    twtml_batch* b = nullptr;
-    TW_TRY(new_csr(ctx, n, d, nnz, &b));
-    int rc = upload_plain(ctx, b->rowptr, rowptr, sizeof(int64_t) * (size_t)(n + 1));
-    if (!rc && nnz) rc = upload_plain(ctx, b->colidx, colidx, sizeof(int32_t) * (size_t)nnz);
-    if (!rc && nnz) rc = upload_plain(ctx, b->vals, vals, sizeof(double) * (size_t)nnz);
-    if (!rc && n) rc = upload_plain(ctx, b->labels, labels, sizeof(double) * (size_t)n);
-    if (!rc) rc = csr_finalize(ctx, b);
+    twtml_batch* b = csr_shell(ctx, n, d, nnz);
+    int rc = csr_ingest(ctx, ctx->lane[0], b, rowptr, colidx, vals, labels, false);
+    if (!rc && cudaStreamSynchronize(ctx->stream) != cudaSuccess) rc = fail(TWTML_E_CUDA, "CSR ingest failed: %s", cudaGetErrorString(cudaGetLastError()));
     if (rc) { batch_free_locked(b); return rc; }
+    *out = b;
+    return 0;
+}
+
+int32_t twtml_batch_from_csr_async(twtml_ctx* ctx, int64_t n, int64_t d, const int64_t* rowptr, const int32_t* colidx, const double* vals,
+                                   const double* labels, twtml_batch** out)
+{
+    int64_t nnz = 0;
+    TW_TRY(check_csr_args(ctx, n, d, rowptr, colidx, vals, labels, out, &nnz));
+    twtml_batch* b = csr_shell(ctx, n, d, nnz);
+    if (int rc = make_ready_event(b)) { Guard g(ctx); batch_free_locked(b); return rc; }
+    submit_ingest(ctx, b, [=]() { return csr_ingest(ctx, ctx->lane[1], b, rowptr, colidx, vals, labels, true); });
     *out = b;
     return 0;
 }
@@ -337,27 +513,29 @@ int32_t twtml_batch_synth_csr(twtml_ctx* ctx, int64_t n, int32_t d_text, uint64_
     if (!ctx || !out) return fail(TWTML_E_INVALID_ARG, "null argument");
     if (n < 0 || d_text < 1) return fail(TWTML_E_INVALID_ARG, "twtml_batch_synth_csr: bad shape");
     Guard g(ctx);
+    IngestLane& lane = ctx->lane[0];
+    std::lock_guard<std::mutex> lane_lock(lane.mu);
     long long *rownnz = nullptr, *rowptr = nullptr;
-    TW_TRY(dev_alloc(ctx, &rownnz, (size_t)n + 1));
-    TW_TRY(dev_alloc(ctx, &rowptr, (size_t)n + 1));
+    TW_TRY(dev_alloc(ctx, lane, &rownnz, (size_t)n + 1));
+    TW_TRY(dev_alloc(ctx, lane, &rowptr, (size_t)n + 1));
     TW_CUDA(cudaMemsetAsync(rownnz, 0, sizeof(long long) * ((size_t)n + 1), ctx->stream));
     if (n > 0) k_synth_csr_count<<<blocks_for(n, 128), 128, 0, ctx->stream>>>(rownnz, n, d_text, seed, row0);
-    int rc = exclusive_sum(ctx, rownnz, rowptr, n + 1);
+    int rc = exclusive_sum(lane, rownnz, rowptr, n + 1);
     long long nnz = 0;
     if (!rc && cudaMemcpyAsync(&nnz, rowptr + n, sizeof(nnz), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) rc = fail(TWTML_E_CUDA, "nnz copy failed");
     cudaStreamSynchronize(ctx->stream);
     pool_free(ctx, rownnz);
     twtml_batch* b = nullptr;
-    if (!rc) rc = new_csr(ctx, n, (int64_t)d_text + 4, nnz, &b);
+    if (!rc) rc = new_csr(ctx, lane, n, (int64_t)d_text + 4, nnz, &b);
     if (!rc) {
         cudaMemcpyAsync(b->rowptr, rowptr, sizeof(long long) * ((size_t)n + 1), cudaMemcpyDeviceToDevice, ctx->stream);
         if (n > 0) k_synth_csr_fill<<<blocks_for(n, 128), 128, 0, ctx->stream>>>(b->rowptr, b->colidx, b->vals, b->labels, n, d_text, seed, row0);
         if (cudaGetLastError() != cudaSuccess) rc = fail(TWTML_E_CUDA, "synthetic CSR generator failed to launch");
     }
-    cudaStreamSynchronize(ctx->stream);
     pool_free(ctx, rowptr);
-    if (!rc) rc = csr_finalize(ctx, b);
-    if (rc) { batch_free_locked(b); return rc; }
+    if (!rc) rc = csr_finalize(ctx, lane, b, false);
+    if (!rc && cudaStreamSynchronize(ctx->stream) != cudaSuccess) rc = fail(TWTML_E_CUDA, "synthetic CSR batch: %s", cudaGetErrorString(cudaGetLastError()));
+    if (rc) { if (b) batch_free_locked(b); return rc; }
     *out = b;
     return 0;
 }
@@ -367,89 +545,31 @@ int32_t twtml_batch_from_tweets(twtml_ctx* ctx, const uint16_t* text_utf16, cons
                                 const uint8_t* is_retweet, int64_t n, int64_t now_ms, int32_t rt_begin, int32_t rt_end,
                                 int32_t num_text_features, uint32_t flags, twtml_batch** out)
 {
-    if (!ctx || !out) return fail(TWTML_E_INVALID_ARG, "null argument");
-    if (n < 0 || num_text_features < 1 || num_text_features > (1 << 30) - 4) return fail(TWTML_E_INVALID_ARG, "twtml_batch_from_tweets: bad sizes");
-    if (n > 0 && (!text_off || !retweet_cnt || !followers || !favourites || !friends || !created_ms || !is_retweet))
-        return fail(TWTML_E_INVALID_ARG, "twtml_batch_from_tweets: null column");
-    const int64_t units = n > 0 ? text_off[n] : 0;
-    if (n > 0 && (text_off[0] != 0 || units < 0 || (units > 0 && !text_utf16))) return fail(TWTML_E_INVALID_ARG, "twtml_batch_from_tweets: bad text offsets");
+    const TweetArgs t{text_utf16, text_off, retweet_cnt, followers, favourites, friends, created_ms, is_retweet, n, now_ms, rt_begin, rt_end, num_text_features, flags};
+    TW_TRY(check_tweet_args(ctx, out, t));
+    int64_t kept = 0;
+    TW_TRY(tweets_precheck(t, &kept));
     Guard g(ctx);
-    const int F = num_text_features;
-    twtml_batch* b = nullptr;
-    if (n == 0) {
-        TW_TRY(new_csr(ctx, 0, (int64_t)F + 4, 0, &b));
-        TW_CUDA(cudaMemsetAsync(b->rowptr, 0, sizeof(long long), ctx->stream));
-        int rc = csr_finalize(ctx, b);
-        if (rc) { batch_free_locked(b); return rc; }
-        *out = b;
-        return 0;
-    }
-    // device copies of the tweet columns
-    uint16_t* d_text = nullptr;
-    long long *d_off = nullptr, *d_created = nullptr, *keep = nullptr, *rownnz = nullptr, *krow = nullptr, *eoff = nullptr;
-    int *d_rc = nullptr, *d_fo = nullptr, *d_fa = nullptr, *d_fr = nullptr, *pair_idx = nullptr, *pair_cnt = nullptr, *d_maxlen = nullptr;
-    uint8_t* d_rt = nullptr;
-    std::vector<void*> owned;
-    auto cleanup = [&]() { for (void* p : owned) pool_free(ctx, p); };
-#define TW_OWN(call, ptrvar) do { int rc_ = (call); if (rc_) { cleanup(); return rc_; } owned.push_back(ptrvar); } while (0)
-#define TW_DO(call) do { int rc_ = (call); if (rc_) { cleanup(); return rc_; } } while (0)
-    TW_OWN(dev_alloc(ctx, &d_text, (size_t)units), d_text);
-    TW_OWN(dev_alloc(ctx, &d_off, (size_t)n + 1), d_off);
-    TW_OWN(dev_alloc(ctx, &d_created, (size_t)n), d_created);
-    TW_OWN(dev_alloc(ctx, &d_rc, (size_t)n), d_rc);
-    TW_OWN(dev_alloc(ctx, &d_fo, (size_t)n), d_fo);
-    TW_OWN(dev_alloc(ctx, &d_fa, (size_t)n), d_fa);
-    TW_OWN(dev_alloc(ctx, &d_fr, (size_t)n), d_fr);
-    TW_OWN(dev_alloc(ctx, &d_rt, (size_t)n), d_rt);
-    TW_OWN(dev_alloc(ctx, &pair_idx, (size_t)units), pair_idx);
-    TW_OWN(dev_alloc(ctx, &pair_cnt, (size_t)units), pair_cnt);
-    TW_OWN(dev_alloc(ctx, &keep, (size_t)n + 1), keep);
-    TW_OWN(dev_alloc(ctx, &rownnz, (size_t)n + 1), rownnz);
-    TW_OWN(dev_alloc(ctx, &krow, (size_t)n + 1), krow);
-    TW_OWN(dev_alloc(ctx, &eoff, (size_t)n + 1), eoff);
-    TW_OWN(dev_alloc(ctx, &d_maxlen, 1), d_maxlen);
-    if (units) TW_DO(upload_plain(ctx, d_text, text_utf16, sizeof(uint16_t) * (size_t)units));
-    TW_DO(upload_plain(ctx, d_off, text_off, sizeof(int64_t) * (size_t)(n + 1)));
-    TW_DO(upload_plain(ctx, d_created, created_ms, sizeof(int64_t) * (size_t)n));
-    TW_DO(upload_plain(ctx, d_rc, retweet_cnt, sizeof(int32_t) * (size_t)n));
-    TW_DO(upload_plain(ctx, d_fo, followers, sizeof(int32_t) * (size_t)n));
-    TW_DO(upload_plain(ctx, d_fa, favourites, sizeof(int32_t) * (size_t)n));
-    TW_DO(upload_plain(ctx, d_fr, friends, sizeof(int32_t) * (size_t)n));
-    TW_DO(upload_plain(ctx, d_rt, is_retweet, (size_t)n));
-
-    cudaMemsetAsync(d_maxlen, 0, sizeof(int), ctx->stream);
-    k_feat_maxlen<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(d_off, n, d_maxlen);
-    int maxlen = 0;
-    cudaMemcpyAsync(&maxlen, d_maxlen, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream);
-    if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) { cleanup(); return fail(TWTML_E_CUDA, "tweet upload failed: %s", cudaGetErrorString(cudaGetLastError())); }
-    if (maxlen > kMaxTerms + 1) { cleanup(); return fail(TWTML_E_INVALID_ARG, "a tweet has %d UTF-16 units; the featuriser takes at most %d", maxlen, kMaxTerms + 1); }
-
-    const uint16_t* lower = nullptr;
-    if (flags & TWTML_FLAG_LOWERCASE) TW_DO(lower_table(ctx, &lower));
-    TweetCols tc{d_text, d_off, d_rc, d_fo, d_fa, d_fr, d_created, d_rt};
-    cudaMemsetAsync(keep + n, 0, sizeof(long long), ctx->stream);
-    cudaMemsetAsync(rownnz + n, 0, sizeof(long long), ctx->stream);
-    const unsigned gridA = (unsigned)std::min<long long>((n + kFeatWarps - 1) / kFeatWarps, (long long)ctx->sm_count * 16);
-    k_feat_terms<<<gridA, kFeatWarps * 32, 0, ctx->stream>>>(tc, n, rt_begin, rt_end, F, lower, pair_idx, pair_cnt, keep, rownnz);
-    TW_DO(exclusive_sum(ctx, keep, krow, n + 1));
-    TW_DO(exclusive_sum(ctx, rownnz, eoff, n + 1));
-    long long tot[2] = {0, 0};
-    cudaMemcpyAsync(&tot[0], krow + n, sizeof(long long), cudaMemcpyDeviceToHost, ctx->stream);
-    cudaMemcpyAsync(&tot[1], eoff + n, sizeof(long long), cudaMemcpyDeviceToHost, ctx->stream);
-    if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) { cleanup(); return fail(TWTML_E_CUDA, "featuriser failed: %s", cudaGetErrorString(cudaGetLastError())); }
-    const long long n_kept = tot[0], nnz = tot[1];
-    TW_DO(new_csr(ctx, n_kept, (int64_t)F + 4, nnz, &b));
-    const unsigned gridB = (unsigned)std::min<long long>((n + 3) / 4, (long long)ctx->sm_count * 16);
-    k_feat_pack<<<gridB, 128, 0, ctx->stream>>>(tc, n, now_ms, F, pair_idx, pair_cnt, keep, krow, rownnz, eoff, b->rowptr, b->colidx, b->vals, b->labels);
-    cudaMemcpyAsync(b->rowptr + n_kept, &tot[1], sizeof(long long), cudaMemcpyHostToDevice, ctx->stream);
-    cudaError_t e = cudaGetLastError();
-    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-    cleanup();
-#undef TW_OWN
-#undef TW_DO
-    int rc = e == cudaSuccess ? 0 : fail(TWTML_E_CUDA, "featuriser pack failed: %s", cudaGetErrorString(e));
-    if (!rc) rc = csr_finalize(ctx, b);
+    twtml_batch* b = csr_shell(ctx, kept, (int64_t)num_text_features + 4, 0);
+    int rc = tweets_ingest(ctx, ctx->lane[0], b, t, false);
+    if (!rc && cudaStreamSynchronize(ctx->stream) != cudaSuccess) rc = fail(TWTML_E_CUDA, "tweet ingest failed: %s", cudaGetErrorString(cudaGetLastError()));
     if (rc) { batch_free_locked(b); return rc; }
+    *out = b;
+    return 0;
+}
+
+int32_t twtml_batch_from_tweets_async(twtml_ctx* ctx, const uint16_t* text_utf16, const int64_t* text_off, const int32_t* retweet_cnt,
+                                      const int32_t* followers, const int32_t* favourites, const int32_t* friends, const int64_t* created_ms,
+                                      const uint8_t* is_retweet, int64_t n, int64_t now_ms, int32_t rt_begin, int32_t rt_end,
+                                      int32_t num_text_features, uint32_t flags, twtml_batch** out)
+{
+    const TweetArgs t{text_utf16, text_off, retweet_cnt, followers, favourites, friends, created_ms, is_retweet, n, now_ms, rt_begin, rt_end, num_text_features, flags};
+    TW_TRY(check_tweet_args(ctx, out, t));
+    int64_t kept = 0;
+    TW_TRY(tweets_precheck(t, &kept));
+    twtml_batch* b = csr_shell(ctx, kept, (int64_t)num_text_features + 4, 0);
+    if (int rc = make_ready_event(b)) { Guard g(ctx); batch_free_locked(b); return rc; }
+    submit_ingest(ctx, b, [=]() { return tweets_ingest(ctx, ctx->lane[1], b, t, true); });
     *out = b;
     return 0;
 }
@@ -460,6 +580,8 @@ int32_t twtml_batch_export_csr(const twtml_batch* b, int64_t* rowptr, int32_t* c
     if (!b->csr) return fail(TWTML_E_INVALID_ARG, "twtml_batch_export_csr on a dense batch");
     twtml_ctx* ctx = b->ctx;
     Guard g(ctx);
+    TW_TRY(settle_batch(ctx, b));
+    if (b->ready) TW_CUDA(cudaStreamWaitEvent(ctx->stream, b->ready, 0));
     TW_CUDA(cudaMemcpyAsync(rowptr, b->rowptr, sizeof(int64_t) * (size_t)(b->n + 1), cudaMemcpyDeviceToHost, ctx->stream));
     if (b->nnz && colidx) TW_CUDA(cudaMemcpyAsync(colidx, b->colidx, sizeof(int32_t) * (size_t)b->nnz, cudaMemcpyDeviceToHost, ctx->stream));
     if (b->nnz && vals) TW_CUDA(cudaMemcpyAsync(vals, b->vals, sizeof(double) * (size_t)b->nnz, cudaMemcpyDeviceToHost, ctx->stream));
