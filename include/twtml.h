@@ -104,6 +104,16 @@ int32_t twtml_create(int32_t device, twtml_ctx** out);
 int32_t twtml_nccl_unique_id(uint8_t* out, int64_t cap);
 int32_t twtml_create_ranked(int32_t device, int32_t rank, int32_t world_size, const uint8_t* nccl_id,
                             int64_t id_bytes, twtml_ctx** out);
+/* One handle that drives several GPUs of this box from ONE host process -- the shape of the reference,
+ * which is a single JVM whose SparkContext (LinearRegression.scala:36) spreads every RDD over local[N]
+ * worker threads.  The group cuts each micro-batch into n_devices contiguous row blocks, keeps a
+ * bit-identical replica of every model on each device and runs the per-iteration exchange between them
+ * through peer memory; the caller uses the returned context exactly like a single-GPU one (same
+ * entry points; output arrays hold all rows, in the caller's row order).  1 <= n_devices <= 8; when
+ * n_devices divides 8 and the batch has a multiple of 8 rows the results equal the single-GPU ones
+ * bit for bit.  twtml_predict_stats_static is not offered on groups. */
+int32_t twtml_create_all(const int32_t* devices, int32_t n_devices, twtml_ctx** out);
+int32_t twtml_device_count(const twtml_ctx* ctx, int32_t* n_devices);
 int32_t twtml_destroy(twtml_ctx* ctx);
 int32_t twtml_rank(const twtml_ctx* ctx, int32_t* rank, int32_t* world_size);
 

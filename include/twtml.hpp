@@ -37,6 +37,13 @@ class Context {
 public:
     explicit Context(int device = 0) { check(twtml_create(device, &h_)); }
     Context(int device, int rank, int world, const uint8_t* nccl_id) { check(twtml_create_ranked(device, rank, world, nccl_id, TWTML_NCCL_ID_BYTES, &h_)); }
+    // one handle over several GPUs of this process (twtml_create_all): the single-JVM shape of the reference
+    explicit Context(const std::vector<int>& devices)
+    {
+        std::vector<int32_t> d(devices.begin(), devices.end());
+        check(twtml_create_all(d.data(), (int32_t)d.size(), &h_));
+    }
+    int deviceCount() const { int32_t n = 0; check(twtml_device_count(h_, &n)); return n; }
     ~Context() { twtml_destroy(h_); }
     Context(const Context&) = delete;
     Context& operator=(const Context&) = delete;

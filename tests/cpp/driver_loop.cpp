@@ -4,6 +4,7 @@
 // written by the test (n, d as int64, then X row-major, then labels); results go to stdout as JSON.
 #include <cstdio>
 #include <cstdlib>
+#include <string>
 #include <vector>
 
 #include "twtml.hpp"
@@ -25,7 +26,18 @@ static bool read_batch(const char* path, int64_t& n, int64_t& d, std::vector<dou
 int main(int argc, char** argv)
 {
     try {
-        twtml::Context ctx(0);
+        // "--devices 0,1,..": drive those GPUs through one group handle (twtml_create_all); default: GPU 0 alone
+        std::vector<int> devices{0};
+        if (argc > 2 && std::string(argv[1]) == "--devices") {
+            devices.clear();
+            for (const char* p = argv[2]; *p;) {
+                devices.push_back((int)std::strtol(p, const_cast<char**>(&p), 10));
+                if (*p == ',') ++p;
+            }
+            argv += 2;
+            argc -= 2;
+        }
+        twtml::Context ctx(devices);
         twtml::StreamingLinearRegressionWithSGD model(ctx);
         try {
             model.latestModel();

@@ -13,7 +13,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO_PATH = os.path.join(HERE, "libtwtml.so")
 HEADER = os.path.join(os.path.dirname(HERE), "include", "twtml.h")
-SOURCES = ["twtml.cu", "twtml_sparse.cu", "twtml_noalloc.cu"]
+SOURCES = ["twtml.cu", "twtml_sparse.cu", "twtml_noalloc.cu", "twtml_group.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC,-fvisibility=hidden", "-shared"]
 
@@ -76,6 +76,8 @@ SIGNATURES = {
     "twtml_create": [_i32, C.POINTER(_vp)],
     "twtml_nccl_unique_id": [_vp, _i64],
     "twtml_create_ranked": [_i32, _i32, _i32, _vp, _i64, C.POINTER(_vp)],
+    "twtml_create_all": [_vp, _i32, C.POINTER(_vp)],
+    "twtml_device_count": [_vp, C.POINTER(_i32)],
     "twtml_destroy": [_vp],
     "twtml_rank": [_vp, C.POINTER(_i32), C.POINTER(_i32)],
     "twtml_profile_enable": [_vp, _i32],

@@ -27,13 +27,27 @@ class Context:
     def __init__(self, device=0, rank=0, world_size=1, nccl_id=None):
         self._h = C.c_void_p()
         L = _lib.lib()
-        if world_size == 1:
+        if isinstance(device, (list, tuple)):               # twtml_create_all: one handle over several GPUs of this process
+            devs = (C.c_int32 * len(device))(*device)
+            check(L.twtml_create_all(devs, len(device), C.byref(self._h)))
+            device = device[0]
+        elif world_size == 1:
             check(L.twtml_create(device, C.byref(self._h)))
         else:
             buf = (C.c_uint8 * _lib.NCCL_ID_BYTES).from_buffer_copy(bytes(nccl_id))
             check(L.twtml_create_ranked(device, rank, world_size, buf, _lib.NCCL_ID_BYTES, C.byref(self._h)))
         self.device, self.rank, self.world_size = device, rank, world_size
         self._children = weakref.WeakSet()     # live Batch / model wrappers: freed before the context goes
+
+    @classmethod
+    def all_devices(cls, devices):
+        """One context driving the listed GPUs from this process (twtml_create_all)."""
+        return cls(list(devices))
+
+    def device_count(self):
+        n = C.c_int32()
+        check(_lib.lib().twtml_device_count(self._h, C.byref(n)))
+        return n.value
 
     @staticmethod
     def nccl_unique_id():

@@ -60,9 +60,16 @@ struct IngestLane {
     cudaEvent_t pin_ev[2] = {nullptr, nullptr};
 };
 
+// One worker thread per member context of a device group (twtml_create_all): the members' calls of one operation run
+// side by side, as they must -- each contains the exchange with the other members.
+struct MemberThreads;
+
 } // namespace twtml
 
 struct twtml_ctx {
+    // a device group (twtml_create_all): this handle only fans calls out to its members, one ranked context per GPU
+    std::vector<twtml_ctx*> members;
+    twtml::MemberThreads* threads = nullptr;
     int device = 0, rank = 0, world = 1, sm_count = 148;
     int spr = twtml::kMaxShards;  // shards per rank
     int nshards = twtml::kMaxShards;
@@ -98,6 +105,7 @@ struct twtml_ctx {
 };
 
 struct twtml_model {
+    std::vector<twtml_model*> members; // group model: one replica per member context (they stay bit-identical)
     twtml_ctx* ctx = nullptr;
     int64_t d = 0;
     double step = 0.1, frac = 1.0, tol = 0.001, reg = 0.0;
@@ -108,6 +116,8 @@ struct twtml_model {
 };
 
 struct twtml_batch {
+    std::vector<twtml_batch*> members;            // group batch: contiguous row blocks, one per member context
+    std::vector<std::vector<int64_t>> owned_i64;  // ... and the re-based row pointers / text offsets the members read
     twtml_ctx* ctx = nullptr;
     bool csr = false;
     int64_t n = 0, d = 0, nnz = 0;
@@ -165,6 +175,42 @@ struct DenseCfg {
     size_t smem;
 };
 int dense_cfg(int64_t d, DenseCfg& c);
+// device groups (twtml_group.cu)
+namespace grp {
+int create_all(const int32_t* devices, int32_t n, twtml_ctx** out);
+int destroy(twtml_ctx* g);
+int profile_enable(twtml_ctx* g, int32_t on);
+int profile_get(const twtml_ctx* g, twtml_profile* out);
+int model_create(twtml_ctx* g, int64_t d, twtml_model** out);
+int model_free(twtml_model* m);
+int set_initial_weights(twtml_model* m, const double* w, int64_t d);
+int get_weights(const twtml_model* m, double* out, int64_t d);
+int from_dense(twtml_ctx* g, int64_t n, int64_t d, const double* X, int64_t ld_x, const double* labels, bool async, twtml_batch** out);
+int dense_begin(twtml_ctx* g, int64_t n, int64_t d, twtml_batch** out);
+int dense_append(twtml_batch* b, int64_t nrows, const double* X, int64_t ld_x, const double* labels);
+int from_csr(twtml_ctx* g, int64_t n, int64_t d, const int64_t* rowptr, const int32_t* colidx, const double* vals, const double* labels,
+             bool async, twtml_batch** out);
+struct TweetCols {
+    const uint16_t* text_utf16;
+    const int64_t* text_off;
+    const int32_t *retweet_cnt, *followers, *favourites, *friends;
+    const int64_t* created_ms;
+    const uint8_t* is_retweet;
+};
+int from_tweets(twtml_ctx* g, const TweetCols& t, int64_t n, int64_t now_ms, int32_t rt_begin, int32_t rt_end, int32_t F, uint32_t flags,
+                bool async, twtml_batch** out);
+int synth_dense(twtml_ctx* g, int64_t n, int64_t d, uint64_t seed, int64_t row0, twtml_batch** out);
+int synth_csr(twtml_ctx* g, int64_t n, int32_t d_text, uint64_t seed, int64_t row0, twtml_batch** out);
+int batch_ready(const twtml_batch* b, int32_t wait, int32_t* ready);
+int batch_info(const twtml_batch* b, int64_t* n, int64_t* d, int64_t* nnz, int32_t* is_csr);
+int export_csr(const twtml_batch* b, int64_t* rowptr, int32_t* colidx, double* vals, double* labels);
+int export_dense(const twtml_batch* b, double* X, double* labels);
+int batch_free(twtml_batch* b);
+int predict(const twtml_model* m, const twtml_batch* b, double* out_pred);
+int predict_stats(const twtml_model* m, const twtml_batch* b, double* out_real, double* out_pred, twtml_stats* out);
+int train(twtml_model* m, const twtml_batch* b, bool with_stats, double* out_real, double* out_pred, twtml_stats* out, double* loss_history,
+          int32_t cap, int32_t* iters_run);
+} // namespace grp
 struct Guard {
     std::lock_guard<std::mutex> lk;
     explicit Guard(twtml_ctx* c) : lk(c->mu) { cudaSetDevice(c->device); }

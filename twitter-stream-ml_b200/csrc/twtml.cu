@@ -942,6 +942,15 @@ static int32_t create_common(int32_t device, int32_t rank, int32_t world, const 
 
 int32_t twtml_create(int32_t device, twtml_ctx** out) { return create_common(device, 0, 1, nullptr, out); }
 
+int32_t twtml_create_all(const int32_t* devices, int32_t n_devices, twtml_ctx** out) { return grp::create_all(devices, n_devices, out); }
+
+int32_t twtml_device_count(const twtml_ctx* ctx, int32_t* n_devices)
+{
+    if (!ctx || !n_devices) return fail(TWTML_E_INVALID_ARG, "null argument");
+    *n_devices = ctx->members.empty() ? 1 : (int32_t)ctx->members.size();
+    return 0;
+}
+
 int32_t twtml_nccl_unique_id(uint8_t* out, int64_t cap)
 {
     static_assert(sizeof(ncclUniqueId) == TWTML_NCCL_ID_BYTES, "ncclUniqueId size");
@@ -963,6 +972,7 @@ int32_t twtml_create_ranked(int32_t device, int32_t rank, int32_t world_size, co
 int32_t twtml_destroy(twtml_ctx* ctx)
 {
     if (!ctx) return 0;
+    if (!ctx->members.empty()) return grp::destroy(ctx);
     {
         std::lock_guard<std::mutex> lk(ctx->mu);
         if (ctx->live_handles.load() != 0)
@@ -1009,6 +1019,7 @@ int32_t twtml_rank(const twtml_ctx* ctx, int32_t* rank, int32_t* world_size)
 int32_t twtml_profile_enable(twtml_ctx* ctx, int32_t on)
 {
     if (!ctx) return fail(TWTML_E_INVALID_ARG, "null context");
+    if (!ctx->members.empty()) return grp::profile_enable(ctx, on);
     ctx->profiling = on != 0;
     return 0;
 }
@@ -1016,6 +1027,7 @@ int32_t twtml_profile_enable(twtml_ctx* ctx, int32_t on)
 int32_t twtml_profile_get(const twtml_ctx* ctx, twtml_profile* out)
 {
     if (!ctx || !out) return fail(TWTML_E_INVALID_ARG, "null argument");
+    if (!ctx->members.empty()) return grp::profile_get(ctx, out);
     *out = ctx->prof;
     return 0;
 }
@@ -1025,6 +1037,7 @@ int32_t twtml_model_create(twtml_ctx* ctx, int64_t num_features, twtml_model** o
 {
     if (!ctx || !out) return fail(TWTML_E_INVALID_ARG, "null argument");
     if (num_features < 1 || num_features > (int64_t)1 << 30) return fail(TWTML_E_INVALID_ARG, "num_features %lld out of range", (long long)num_features);
+    if (!ctx->members.empty()) return grp::model_create(ctx, num_features, out);
     Guard g(ctx);
     twtml_model* m = new twtml_model();
     m->ctx = ctx;
@@ -1041,6 +1054,7 @@ int32_t twtml_model_create(twtml_ctx* ctx, int64_t num_features, twtml_model** o
 int32_t twtml_model_free(twtml_model* m)
 {
     if (!m) return 0;
+    if (!m->members.empty()) return grp::model_free(m);
     {
         Guard g(m->ctx);
         cudaStreamSynchronize(m->ctx->stream);
@@ -1054,12 +1068,14 @@ int32_t twtml_model_free(twtml_model* m)
 int32_t twtml_set_step_size(twtml_model* m, double v)
 {
     if (!m) return fail(TWTML_E_INVALID_ARG, "null model");
+    for (twtml_model* mm : m->members) TW_TRY(twtml_set_step_size(mm, v));
     m->step = v;
     return 0;
 }
 int32_t twtml_set_num_iterations(twtml_model* m, int32_t v)
 {
     if (!m) return fail(TWTML_E_INVALID_ARG, "null model");
+    for (twtml_model* mm : m->members) TW_TRY(twtml_set_num_iterations(mm, v));
     if (v < 0) return fail(TWTML_E_INVALID_ARG, "numIterations must be >= 0");
     m->num_iter = v;
     return 0;
@@ -1067,12 +1083,14 @@ int32_t twtml_set_num_iterations(twtml_model* m, int32_t v)
 int32_t twtml_set_mini_batch_fraction(twtml_model* m, double v)
 {
     if (!m) return fail(TWTML_E_INVALID_ARG, "null model");
+    for (twtml_model* mm : m->members) TW_TRY(twtml_set_mini_batch_fraction(mm, v));
     m->frac = v;
     return 0;
 }
 int32_t twtml_set_convergence_tol(twtml_model* m, double v)
 {
     if (!m) return fail(TWTML_E_INVALID_ARG, "null model");
+    for (twtml_model* mm : m->members) TW_TRY(twtml_set_convergence_tol(mm, v));
     if (!(v >= 0.0 && v <= 1.0)) return fail(TWTML_E_INVALID_ARG, "convergenceTol must be in [0, 1]"); // require() in GradientDescent [U]
     m->tol = v;
     return 0;
@@ -1080,12 +1098,14 @@ int32_t twtml_set_convergence_tol(twtml_model* m, double v)
 int32_t twtml_set_reg_param(twtml_model* m, double v)
 {
     if (!m) return fail(TWTML_E_INVALID_ARG, "null model");
+    for (twtml_model* mm : m->members) TW_TRY(twtml_set_reg_param(mm, v));
     m->reg = v;
     return 0;
 }
 int32_t twtml_set_updater(twtml_model* m, int32_t kind)
 {
     if (!m) return fail(TWTML_E_INVALID_ARG, "null model");
+    for (twtml_model* mm : m->members) TW_TRY(twtml_set_updater(mm, kind));
     if (kind < 0 || kind > 2) return fail(TWTML_E_INVALID_ARG, "updater must be 0 (Simple), 1 (SquaredL2) or 2 (L1)");
     m->updater = kind;
     return 0;
@@ -1095,6 +1115,7 @@ int32_t twtml_set_initial_weights(twtml_model* m, const double* w, int64_t d)
 {
     if (!m || !w) return fail(TWTML_E_INVALID_ARG, "null argument");
     if (d != m->d) return fail(TWTML_E_SHAPE_MISMATCH, "setInitialWeights: got %lld values for %lld features", (long long)d, (long long)m->d);
+    if (!m->members.empty()) return grp::set_initial_weights(m, w, d);
     Guard g(m->ctx);
     memcpy(m->h_w.data(), w, sizeof(double) * (size_t)d);
     TW_CUDA(cudaMemcpyAsync(m->d_w, m->h_w.data(), sizeof(double) * (size_t)d, cudaMemcpyHostToDevice, m->ctx->stream));
@@ -1108,6 +1129,7 @@ int32_t twtml_get_weights(const twtml_model* m, double* out, int64_t d)
     if (!m || !out) return fail(TWTML_E_INVALID_ARG, "null argument");
     if (!m->initialized) return fail(TWTML_E_NOT_INITIALIZED, "Model must be initialized before starting prediction.");
     if (d != m->d) return fail(TWTML_E_SHAPE_MISMATCH, "get_weights: buffer of %lld for %lld features", (long long)d, (long long)m->d);
+    if (!m->members.empty()) return grp::get_weights(m, out, d);
     memcpy(out, m->h_w.data(), sizeof(double) * (size_t)d);
     return 0;
 }
@@ -1182,6 +1204,7 @@ int32_t twtml_batch_from_dense(twtml_ctx* ctx, int64_t n, int64_t d, const doubl
 {
     if (!ctx || !out) return fail(TWTML_E_INVALID_ARG, "null argument");
     if (n < 0 || d < 1 || (n > 0 && (!X || !labels)) || ld_x < d) return fail(TWTML_E_INVALID_ARG, "twtml_batch_from_dense: bad shape or null data");
+    if (!ctx->members.empty()) return grp::from_dense(ctx, n, d, X, ld_x, labels, false, out);
     Guard g(ctx);
     twtml_batch* b = nullptr;
     TW_TRY(new_dense(ctx, n, d, &b));
@@ -1229,6 +1252,7 @@ int32_t twtml_batch_from_dense_async(twtml_ctx* ctx, int64_t n, int64_t d, const
 {
     if (!ctx || !out) return fail(TWTML_E_INVALID_ARG, "null argument");
     if (n < 0 || d < 1 || (n > 0 && (!X || !labels)) || ld_x < d) return fail(TWTML_E_INVALID_ARG, "twtml_batch_from_dense_async: bad shape or null data");
+    if (!ctx->members.empty()) return grp::from_dense(ctx, n, d, X, ld_x, labels, true, out);
     // only page-locked host memory can be copied without a host-side staging pass
     if (n > 0 && (!page_locked(X) || !page_locked(labels))) return twtml_batch_from_dense(ctx, n, d, X, ld_x, labels, out);
     Guard g(ctx);
@@ -1245,6 +1269,7 @@ int32_t twtml_batch_dense_begin(twtml_ctx* ctx, int64_t n, int64_t d, twtml_batc
 {
     if (!ctx || !out) return fail(TWTML_E_INVALID_ARG, "null argument");
     if (n < 0 || d < 1) return fail(TWTML_E_INVALID_ARG, "twtml_batch_dense_begin: bad shape");
+    if (!ctx->members.empty()) return grp::dense_begin(ctx, n, d, out);
     Guard g(ctx);
     return begin_dense_async(ctx, n, d, out);
 }
@@ -1252,6 +1277,10 @@ int32_t twtml_batch_dense_begin(twtml_ctx* ctx, int64_t n, int64_t d, twtml_batc
 int32_t twtml_batch_dense_append(twtml_batch* b, int64_t nrows, const double* X, int64_t ld_x, const double* labels)
 {
     if (!b) return fail(TWTML_E_INVALID_ARG, "null batch");
+    if (!b->members.empty()) {
+        if (nrows < 0 || (nrows > 0 && (!X || !labels)) || ld_x < b->d) return fail(TWTML_E_INVALID_ARG, "twtml_batch_dense_append: bad shape or null data");
+        return grp::dense_append(b, nrows, X, ld_x, labels);
+    }
     if (b->csr || !b->ready) return fail(TWTML_E_INVALID_ARG, "twtml_batch_dense_append: not a batch from twtml_batch_dense_begin");
     if (nrows < 0 || (nrows > 0 && (!X || !labels)) || ld_x < b->d) return fail(TWTML_E_INVALID_ARG, "twtml_batch_dense_append: bad shape or null data");
     if (b->rows_appended + nrows > b->n)
@@ -1265,6 +1294,7 @@ int32_t twtml_batch_dense_append(twtml_batch* b, int64_t nrows, const double* X,
 int32_t twtml_batch_ready(const twtml_batch* b, int32_t wait, int32_t* ready)
 {
     if (!b) return fail(TWTML_E_INVALID_ARG, "null batch");
+    if (!b->members.empty()) return grp::batch_ready(b, wait, ready);
     int r = 1;
     if (b->has_pending) { // asynchronous CSR / tweet ingest: the worker's verdict first
         if (!wait && b->pending.wait_for(std::chrono::seconds(0)) != std::future_status::ready) {
@@ -1291,6 +1321,7 @@ int32_t twtml_batch_synth_dense(twtml_ctx* ctx, int64_t n, int64_t d, uint64_t s
 {
     if (!ctx || !out) return fail(TWTML_E_INVALID_ARG, "null argument");
     if (n < 0 || d < 1) return fail(TWTML_E_INVALID_ARG, "twtml_batch_synth_dense: bad shape");
+    if (!ctx->members.empty()) return grp::synth_dense(ctx, n, d, seed, row0, out);
     Guard g(ctx);
     twtml_batch* b = nullptr;
     TW_TRY(new_dense(ctx, n, d, &b));
@@ -1310,6 +1341,7 @@ int32_t twtml_batch_synth_dense(twtml_ctx* ctx, int64_t n, int64_t d, uint64_t s
 int32_t twtml_batch_rows(const twtml_batch* b, int64_t* n)
 {
     if (!b || !n) return fail(TWTML_E_INVALID_ARG, "null argument");
+    if (!b->members.empty()) return grp::batch_info(b, n, nullptr, nullptr, nullptr);
     *n = b->n;
     return 0;
 }
@@ -1317,6 +1349,7 @@ int32_t twtml_batch_rows(const twtml_batch* b, int64_t* n)
 int32_t twtml_batch_info(const twtml_batch* b, int64_t* n, int64_t* d, int64_t* nnz, int32_t* is_csr)
 {
     if (!b) return fail(TWTML_E_INVALID_ARG, "null batch");
+    if (!b->members.empty()) return grp::batch_info(b, n, d, nnz, is_csr);
     if (nnz && b->has_pending) { // only the finished ingest knows how many entries a featurised batch has
         const int rc = b->pending.get();
         if (rc) return fail(rc, "asynchronous ingest failed: %s", b->pending_err.c_str());
@@ -1332,6 +1365,7 @@ int32_t twtml_batch_export_dense(const twtml_batch* b, double* X, double* labels
 {
     if (!b || !X || !labels) return fail(TWTML_E_INVALID_ARG, "null argument");
     if (b->csr) return fail(TWTML_E_INVALID_ARG, "twtml_batch_export_dense on a CSR batch");
+    if (!b->members.empty()) return grp::export_dense(b, X, labels);
     if (b->n == 0) return 0;
     twtml_ctx* ctx = b->ctx;
     Guard g(ctx);
@@ -1349,6 +1383,7 @@ int32_t twtml_batch_export_dense(const twtml_batch* b, double* X, double* labels
 int32_t twtml_batch_free(twtml_batch* b)
 {
     if (!b) return 0;
+    if (!b->members.empty()) return grp::batch_free(b);
     Guard g(b->ctx);
     batch_free_locked(b);
     return 0;
@@ -1359,6 +1394,7 @@ int32_t twtml_predict(const twtml_model* m, const twtml_batch* b, double* out_pr
 {
     TW_TRY(check_pair(m, b, "prediction"));
     if (!out_pred && b->n > 0) return fail(TWTML_E_INVALID_ARG, "twtml_predict: out_pred is null");
+    if (!m->members.empty()) return grp::predict(m, b, out_pred);
     twtml_ctx* ctx = m->ctx;
     Guard g(ctx);
     TW_TRY(wait_ready(ctx, b));
@@ -1375,6 +1411,7 @@ int32_t twtml_predict_stats(const twtml_model* m, const twtml_batch* b, double* 
 {
     TW_TRY(check_pair(m, b, "prediction"));
     if (!out) return fail(TWTML_E_INVALID_ARG, "twtml_predict_stats: out is null");
+    if (!m->members.empty()) return grp::predict_stats(m, b, out_real, out_pred_rounded, out);
     Guard g(m->ctx);
     return do_predict_stats(m, b, out_real, out_pred_rounded, out);
 }
@@ -1382,6 +1419,7 @@ int32_t twtml_predict_stats(const twtml_model* m, const twtml_batch* b, double* 
 int32_t twtml_train_on_batch(twtml_model* m, const twtml_batch* b, double* loss_history, int32_t cap, int32_t* iters_run)
 {
     TW_TRY(check_pair(m, b, "training"));
+    if (!m->members.empty()) return grp::train(m, b, false, nullptr, nullptr, nullptr, loss_history, cap, iters_run);
     Guard g(m->ctx);
     return do_train(m, b, false, nullptr, nullptr, nullptr, loss_history, cap, iters_run);
 }
@@ -1391,6 +1429,7 @@ int32_t twtml_step(twtml_model* m, const twtml_batch* b, double* out_real, doubl
 {
     TW_TRY(check_pair(m, b, "training"));
     if (!out) return fail(TWTML_E_INVALID_ARG, "twtml_step: out is null");
+    if (!m->members.empty()) return grp::train(m, b, true, out_real, out_pred_rounded, out, loss_history, cap, iters_run);
     Guard g(m->ctx);
     return do_train(m, b, true, out_real, out_pred_rounded, out, loss_history, cap, iters_run);
 }

@@ -92,7 +92,7 @@ extern "C" int32_t twtml_predict_stats_static(const twtml_model* m, const twtml_
     if (!m->initialized) return fail(TWTML_E_NOT_INITIALIZED, "Model must be initialized before starting prediction.");
     if (m->d != b->d) return fail(TWTML_E_SHAPE_MISMATCH, "twtml_predict_stats_static: model has %lld features, batch has %lld", (long long)m->d, (long long)b->d);
     twtml_ctx* ctx = m->ctx;
-    if (ctx->world != 1) return fail(TWTML_E_INVALID_ARG, "twtml_predict_stats_static: single-GPU contexts only");
+    if (ctx->world != 1 || !ctx->members.empty()) return fail(TWTML_E_INVALID_ARG, "twtml_predict_stats_static: single-GPU contexts only");
     if (b->csr) return fail(TWTML_E_INVALID_ARG, "twtml_predict_stats_static: dense batches only");
     if (b->plan.nblocks > kMaxBlocks)
         return fail(TWTML_E_INVALID_ARG, "twtml_predict_stats_static: batch has %lld row blocks, the static scratch holds %d (about %lld rows); use twtml_predict_stats",

@@ -487,6 +487,7 @@ int32_t twtml_batch_from_csr(twtml_ctx* ctx, int64_t n, int64_t d, const int64_t
 {
     int64_t nnz = 0;
     TW_TRY(check_csr_args(ctx, n, d, rowptr, colidx, vals, labels, out, &nnz));
+    if (!ctx->members.empty()) return grp::from_csr(ctx, n, d, rowptr, colidx, vals, labels, false, out);
     Guard g(ctx);
     twtml_batch* b = csr_shell(ctx, n, d, nnz);
     int rc = csr_ingest(ctx, ctx->lane[0], b, rowptr, colidx, vals, labels, false);
@@ -501,6 +502,7 @@ int32_t twtml_batch_from_csr_async(twtml_ctx* ctx, int64_t n, int64_t d, const i
 {
     int64_t nnz = 0;
     TW_TRY(check_csr_args(ctx, n, d, rowptr, colidx, vals, labels, out, &nnz));
+    if (!ctx->members.empty()) return grp::from_csr(ctx, n, d, rowptr, colidx, vals, labels, true, out);
     twtml_batch* b = csr_shell(ctx, n, d, nnz);
     if (int rc = make_ready_event(b)) { Guard g(ctx); batch_free_locked(b); return rc; }
     submit_ingest(ctx, b, [=]() { return csr_ingest(ctx, ctx->lane[1], b, rowptr, colidx, vals, labels, true); });
@@ -512,6 +514,7 @@ int32_t twtml_batch_synth_csr(twtml_ctx* ctx, int64_t n, int32_t d_text, uint64_
 {
     if (!ctx || !out) return fail(TWTML_E_INVALID_ARG, "null argument");
     if (n < 0 || d_text < 1) return fail(TWTML_E_INVALID_ARG, "twtml_batch_synth_csr: bad shape");
+    if (!ctx->members.empty()) return grp::synth_csr(ctx, n, d_text, seed, row0, out);
     Guard g(ctx);
     IngestLane& lane = ctx->lane[0];
     std::lock_guard<std::mutex> lane_lock(lane.mu);
@@ -547,6 +550,9 @@ int32_t twtml_batch_from_tweets(twtml_ctx* ctx, const uint16_t* text_utf16, cons
 {
     const TweetArgs t{text_utf16, text_off, retweet_cnt, followers, favourites, friends, created_ms, is_retweet, n, now_ms, rt_begin, rt_end, num_text_features, flags};
     TW_TRY(check_tweet_args(ctx, out, t));
+    if (!ctx->members.empty())
+        return grp::from_tweets(ctx, grp::TweetCols{text_utf16, text_off, retweet_cnt, followers, favourites, friends, created_ms, is_retweet}, n, now_ms,
+                                rt_begin, rt_end, num_text_features, flags, false, out);
     int64_t kept = 0;
     TW_TRY(tweets_precheck(t, &kept));
     Guard g(ctx);
@@ -565,6 +571,9 @@ int32_t twtml_batch_from_tweets_async(twtml_ctx* ctx, const uint16_t* text_utf16
 {
     const TweetArgs t{text_utf16, text_off, retweet_cnt, followers, favourites, friends, created_ms, is_retweet, n, now_ms, rt_begin, rt_end, num_text_features, flags};
     TW_TRY(check_tweet_args(ctx, out, t));
+    if (!ctx->members.empty())
+        return grp::from_tweets(ctx, grp::TweetCols{text_utf16, text_off, retweet_cnt, followers, favourites, friends, created_ms, is_retweet}, n, now_ms,
+                                rt_begin, rt_end, num_text_features, flags, true, out);
     int64_t kept = 0;
     TW_TRY(tweets_precheck(t, &kept));
     twtml_batch* b = csr_shell(ctx, kept, (int64_t)num_text_features + 4, 0);
@@ -578,6 +587,7 @@ int32_t twtml_batch_export_csr(const twtml_batch* b, int64_t* rowptr, int32_t* c
 {
     if (!b || !rowptr) return fail(TWTML_E_INVALID_ARG, "null argument");
     if (!b->csr) return fail(TWTML_E_INVALID_ARG, "twtml_batch_export_csr on a dense batch");
+    if (!b->members.empty()) return grp::export_csr(b, rowptr, colidx, vals, labels);
     twtml_ctx* ctx = b->ctx;
     Guard g(ctx);
     TW_TRY(settle_batch(ctx, b));
