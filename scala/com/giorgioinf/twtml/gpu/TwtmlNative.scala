@@ -8,6 +8,8 @@ trait TwtmlNative extends Library {
   def twtml_abi_version(): Int
   def twtml_last_error(buf: Array[Byte], cap: Long): Int
   def twtml_create(device: Int, out: PointerByReference): Int
+  def twtml_create_all(devices: Array[Int], nDevices: Int, out: PointerByReference): Int
+  def twtml_device_count(ctx: Pointer, n: IntByReference): Int
   def twtml_nccl_unique_id(out: Array[Byte], cap: Long): Int
   def twtml_create_ranked(device: Int, rank: Int, world: Int, id: Array[Byte], idBytes: Long, out: PointerByReference): Int
   def twtml_destroy(ctx: Pointer): Int
@@ -22,10 +24,17 @@ trait TwtmlNative extends Library {
   def twtml_batch_from_tweets(ctx: Pointer, textUtf16: Array[Char], textOff: Array[Long], retweetCnt: Array[Int],
       followers: Array[Int], favourites: Array[Int], friends: Array[Int], createdMs: Array[Long], isRetweet: Array[Byte],
       n: Long, nowMs: Long, rtBegin: Int, rtEnd: Int, numTextFeatures: Int, flags: Int, out: PointerByReference): Int
-  def twtml_batch_from_csr(ctx: Pointer, n: Long, d: Long, rowptr: Array[Long], colidx: Array[Int], vals: Array[Double],
-      labels: Array[Double], out: PointerByReference): Int
-  def twtml_batch_from_dense(ctx: Pointer, n: Long, d: Long, x: Array[Double], ldX: Long, labels: Array[Double],
+  // the packed batch travels in direct NIO buffers (JNA passes a direct Buffer as the address of its memory: no copy on
+  // the way into the call)
+  def twtml_batch_from_csr(ctx: Pointer, n: Long, d: Long, rowptr: java.nio.LongBuffer, colidx: java.nio.IntBuffer,
+      vals: java.nio.DoubleBuffer, labels: java.nio.DoubleBuffer, out: PointerByReference): Int
+  def twtml_batch_from_dense(ctx: Pointer, n: Long, d: Long, x: java.nio.DoubleBuffer, ldX: Long, labels: java.nio.DoubleBuffer,
       out: PointerByReference): Int
+  def twtml_batch_from_csr_async(ctx: Pointer, n: Long, d: Long, rowptr: java.nio.LongBuffer, colidx: java.nio.IntBuffer,
+      vals: java.nio.DoubleBuffer, labels: java.nio.DoubleBuffer, out: PointerByReference): Int
+  def twtml_batch_from_dense_async(ctx: Pointer, n: Long, d: Long, x: java.nio.DoubleBuffer, ldX: Long, labels: java.nio.DoubleBuffer,
+      out: PointerByReference): Int
+  def twtml_batch_ready(b: Pointer, waitFor: Int, ready: IntByReference): Int
   def twtml_batch_rows(b: Pointer, n: LongByReference): Int
   def twtml_batch_free(b: Pointer): Int
   def twtml_predict(m: Pointer, b: Pointer, outPred: Array[Double]): Int
