@@ -366,6 +366,225 @@ __global__ void __launch_bounds__(kNarrowThreadsMax, 1) k_csr_narrow(const Narro
     }
 }
 
+// ---- rows in pairs: models of at most kNarrowPairMaxD columns ------------------------------------------------
+// The row loop above is bound by its own length, not by memory: ~190 instructions and ~2000 cycles per row and warp,
+// one row at a time (profiles/r01_SUMMARY.md).  Here a warp takes two ADJACENT rows at once, one per half-warp: the
+// same instruction stream serves both rows (half the instructions per row), 16-lane slots waste fewer lanes on rows
+// of ~70 entries (80 lane slots instead of 96), the butterfly has four steps, and twice as many rows are in flight
+// per SM with the same sixteen accumulators.  The two rows of a pair share their warp's accumulator, so the second
+// half of the work runs in two rounds -- row A's lanes add diff_A * x_A, then row B's lanes add diff_B * x_B -- which
+// also keeps the per-column order of additions fixed (row order), hence bit-reproducible.  A pair of rows of at
+// most kNarrowPairMaxD entries each spans at most three tiles, which is what the four-tile ring allows.
+constexpr int kNarrowPairMaxD = 1024;
+constexpr int kPairK = 5; // 16-lane slots of a row kept in registers between the two halves (80 entries)
+
+template <int MODE>
+__global__ void __launch_bounds__(kNarrowThreadsMax, 1) k_csr_narrow_pairs(const NarrowArgs a)
+{
+    constexpr bool kTrain = (MODE == MODE_TRAIN || MODE == MODE_TRAIN_STATS);
+    constexpr bool kStats = (MODE == MODE_TRAIN_STATS || MODE == MODE_PREDICT_STATS);
+    constexpr bool kPerRow = kStats || MODE == MODE_PREDICT;
+    constexpr unsigned kMask = kNarrowRing - 1;
+    if (kTrain && a.state->done) return;
+
+    extern __shared__ __align__(128) unsigned char smem[];
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem);
+    uint64_t* empty = full + kNarrowStages;
+    double* val_ring = reinterpret_cast<double*>(smem + 128);
+    int* col_ring = reinterpret_cast<int*>(smem + 128 + (size_t)kNarrowRing * 8);
+    double* w_s = reinterpret_cast<double*>(smem + kNarrowRingBytes);
+    double* sred = w_s + a.d;
+    double* gacc = sred + kNarrowRedDoubles;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5, W = a.warps, d = a.d;
+    const int half = lane >> 4, q = lane & 15;
+    const unsigned long long iter_seed =
+        splitmix64((unsigned long long)(42 + (a.iter_override > 0 ? a.iter_override : (kTrain ? a.state->iter : 0))));
+    const bool sampling = kTrain && a.frac < 1.0;
+
+    const long long C0 = a.bounds[blockIdx.x], C1 = a.bounds[blockIdx.x + 1];
+    const int E0 = (int)a.rowptr[C0], E1 = (int)a.rowptr[C1], Ea = E0 & ~3;
+    const int ntiles = E1 > E0 ? (E1 - Ea + kNarrowTile - 1) >> kNarrowTileLog : 0;
+    const uint64_t policy = l2_evict_first_policy();
+    auto fill = [&](int tl) { // producer lane only
+        const int s = tl & (kNarrowStages - 1);
+        const int start = Ea + tl * kNarrowTile;
+        const int cnt = min(kNarrowTile, (E1 - start + 3) & ~3);
+        mbar_expect_tx(&full[s], (uint32_t)cnt * 12u);
+        tma_load_1d(val_ring + s * kNarrowTile, a.vals + start, (uint32_t)cnt * 8u, &full[s], policy);
+        tma_load_1d(col_ring + s * kNarrowTile, a.colidx + start, (uint32_t)cnt * 4u, &full[s], policy);
+    };
+    if (t == W * 32) {
+        for (int s = 0; s < kNarrowStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], (uint32_t)W); }
+        mbar_fence_init();
+        for (int tl = 0; tl < min(ntiles, kNarrowStages); ++tl) fill(tl);
+    }
+    for (int j = t; j < d; j += blockDim.x) w_s[j] = a.w[j];
+    if (kTrain)
+        for (int j = t; j < W * d; j += blockDim.x) gacc[j] = 0.0;
+    __syncthreads();
+
+    double my_loss = 0.0, my_cnt = 0.0;
+    Stat7 my_stat;
+    stat_zero(my_stat);
+
+    if (warp == W) {
+        if (lane == 0) {
+            for (int tl = kNarrowStages; tl < ntiles; ++tl) {
+                mbar_wait(&empty[tl & (kNarrowStages - 1)], (uint32_t)((tl / kNarrowStages - 1) & 1));
+                fill(tl);
+            }
+        }
+    } else {
+        // warp w takes the CTA's row pairs w, w + W, ...: local pair j is rows C0 + 2 (w + W j) and the one after it
+        const int span = (int)(C1 - C0), npairs = (span + 1) >> 1;
+        const int P1 = npairs > warp ? (npairs - warp + W - 1) / W : 0;
+        auto pairrow = [&](int j) { return C0 + 2ll * (warp + W * j); };
+        const uint32_t ws = keep_u32(smem_u32(w_s)), gs = keep_u32(smem_u32(gacc + (size_t)warp * d)), vs = keep_u32(smem_u32(val_ring)),
+                       cs = keep_u32(smem_u32(col_ring)), fb = keep_u32(smem_u32(full)), eb = keep_u32(smem_u32(empty));
+        unsigned waited = 0, released = 0;
+        auto wait_tile = [&]() {
+            mbar_wait_addr(fb + 8u * (waited & (kNarrowStages - 1)), (waited / kNarrowStages) & 1u);
+            ++waited;
+        };
+        auto release_tile = [&]() { // only a tile that was observed full
+            if (waited <= released) wait_tile();
+            if (lane == 0) mbar_arrive_addr(eb + 8u * (released & (kNarrowStages - 1)));
+            ++released;
+        };
+        // Row pointers and labels of 16 pairs at a time: lane (16 h + i) holds those of row h of pair 16 c + i, for the
+        // current chunk c and the next one; a half-warp fetches its row's by one shuffle each.
+        int lo1 = 0, hi1 = 0, lo2 = 0, hi2 = 0;
+        double y1 = 0.0, y2 = 0.0;
+        auto load_chunk = [&](int b0, int& lo, int& hi, double& y) {
+            const int j0 = b0 + q;
+            const long long row = pairrow(j0 < P1 ? j0 : 0) + half;
+            const bool in = j0 < P1 && row < C1; // the last pair of an odd range has no second row: empty, at the stretch's end
+            lo = (int)a.rowptr[in ? row : C1];
+            hi = (int)a.rowptr[in ? row + 1 : C1];
+            y = a.labels[in ? row : C0];
+        };
+        if (P1 > 0) load_chunk(0, lo2, hi2, y2);
+        for (int j = 0; j < P1; ++j) {
+            const int sel = j & 15;
+            if (sel == 0) {
+                lo1 = lo2;
+                hi1 = hi2;
+                y1 = y2;
+                if (j + 16 < P1) load_chunk(j + 16, lo2, hi2, y2);
+            }
+            const int src = (lane & 16) | sel;
+            const int kb = __shfl_sync(0xffffffffu, lo1, src), ke = __shfl_sync(0xffffffffu, hi1, src);
+            const double y = __shfl_sync(0xffffffffu, y1, src);
+            const int pkb = __shfl_sync(0xffffffffu, lo1, sel), pke = __shfl_sync(0xffffffffu, hi1, 16 | sel); // the pair's stretch
+            const int ne = ke - kb;
+            const long long row = pairrow(j) + half;
+            const bool valid = row < C1;
+            if (pke > pkb) {
+                const unsigned tb = (unsigned)(pkb - Ea) >> kNarrowTileLog, te = (unsigned)(pke - 1 - Ea) >> kNarrowTileLog;
+#pragma unroll 1
+                while (released < tb) release_tile();
+#pragma unroll 1
+                while (waited <= te) wait_tile();
+            }
+            // w . x of both rows: 16-lane slots, the first kPairK of them stay in registers for the second half
+            const unsigned o0 = (unsigned)(kb - Ea + q);
+            int c[kPairK];
+            double v[kPairK];
+            double acc = 0.0;
+#pragma unroll
+            for (int i = 0; i < kPairK; ++i) {
+                const unsigned idx = (o0 + 16u * i) & kMask;
+                c[i] = 0;
+                v[i] = 0.0;
+                narrow_slot_dot(q + 16 * i < ne, cs + 4u * idx, vs + 8u * idx, ws, c[i], v[i], acc);
+            }
+            const int ne_max = max(ne, __shfl_xor_sync(0xffffffffu, ne, 16)); // both halves run the tail loops together
+#pragma unroll 1
+            for (int k = q + 16 * kPairK; k < ne_max; k += 16) {
+                if (k < ne) {
+                    const unsigned idx = (unsigned)(kb - Ea + k) & kMask;
+                    acc = fma(lds_f64(vs + 8u * idx), lds_f64(ws + 8u * (unsigned)lds_s32(cs + 4u * idx)), acc);
+                }
+            }
+#pragma unroll
+            for (int mk = 8; mk >= 1; mk >>= 1) acc += shfl_xor_f64(acc, mk); // inside the half-warp: the same bits in its 16 lanes
+            if (kTrain) {
+                const bool live = valid && (!sampling || row_sampled(iter_seed, a.row0_global + (unsigned long long)row, a.frac));
+                const double diff = acc - y;
+                if (live) {
+                    my_loss += diff * diff / 2.0;
+                    my_cnt += 1.0;
+                }
+#pragma unroll 1
+                for (int rnd = 0; rnd < 2; ++rnd) { // row A's additions, then row B's: they may meet on a column
+                    const bool mine = live && half == rnd;
+#pragma unroll
+                    for (int i = 0; i < kPairK; ++i) narrow_slot_add(mine && q + 16 * i < ne, c[i], v[i], diff, gs);
+#pragma unroll 1
+                    for (int k = q + 16 * kPairK; k < ne_max; k += 16) {
+                        if (mine && k < ne) {
+                            const unsigned idx = (unsigned)(kb - Ea + k) & kMask;
+                            const uint32_t ga = gs + 8u * (unsigned)lds_s32(cs + 4u * idx);
+                            sts_f64(ga, fma(diff, lds_f64(vs + 8u * idx), lds_f64(ga)));
+                        }
+                    }
+                    __syncwarp();
+                }
+            }
+            if (kPerRow && q == 0 && valid) {
+                if (kStats) {
+                    const double pr = round_half_up(acc + 0.0);
+                    stat_add(my_stat, y, pr);
+                    if (a.out_pred) a.out_pred[row] = pr;
+                    if (a.out_real) a.out_real[row] = y;
+                } else {
+                    a.out_pred[row] = acc + 0.0;
+                }
+            }
+        }
+#pragma unroll 1
+        while (released < (unsigned)ntiles) release_tile();
+        // a warp's (lossSum, count): row A's chain plus row B's chain
+        my_loss += shfl_xor_f64(my_loss, 16);
+        my_cnt += shfl_xor_f64(my_cnt, 16);
+    }
+    __syncthreads();
+
+    if (kTrain) {
+        double* out = a.partials + (long long)blockIdx.x * (d + 2);
+        for (int j = t; j < d; j += blockDim.x) {
+            double s = gacc[j];
+            for (int qq = 1; qq < W; ++qq) s += gacc[(size_t)qq * d + j];
+            out[j] = s;
+        }
+        if (lane == 0 && warp < W) { sred[2 * warp] = my_loss; sred[2 * warp + 1] = my_cnt; }
+        __syncthreads();
+        if (t == 0) {
+            double ls = 0.0, cn = 0.0;
+            for (int qq = 0; qq < W; ++qq) { ls += sred[2 * qq]; cn += sred[2 * qq + 1]; }
+            out[d] = ls;
+            out[d + 1] = cn;
+        }
+    }
+    if (kStats) {
+        double* sst = sred + 2 * kNarrowMaxWarps;
+        if (q != 0) stat_zero(my_stat);
+        narrow_warp_stat(my_stat);
+        if (lane == 0 && warp < W) stat_store(sst + warp * kStatStride, my_stat);
+        __syncthreads();
+        if (t == 0) {
+            Stat7 tot;
+            stat_zero(tot);
+            for (int qq = 0; qq < W; ++qq) {
+                Stat7 s2;
+                stat_load(s2, sst + qq * kStatStride);
+                stat_merge(tot, s2);
+            }
+            stat_store(a.stat_partials + (long long)blockIdx.x * kStatStride, tot);
+        }
+    }
+}
+
 // ---- ingest: first row of every CTA, balancing entries + kNarrowRowCost per row (a row's fixed work -- bounds, butterfly,
 // bookkeeping -- costs about as much as that many entries)
 static __global__ void k_narrow_bounds(const long long* __restrict__ rowptr, long long n, long long G, long long* __restrict__ bounds)

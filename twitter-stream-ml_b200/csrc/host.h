@@ -87,6 +87,7 @@ struct twtml_ctx {
     int* host_done = nullptr;     // mapped pinned word: the update kernel sets it when a training loop has ended
     int* host_done_dev = nullptr; // ... its device alias
     unsigned smem_attr_done = 0; // dense iteration-kernel forms whose dynamic shared-memory limit is raised
+    unsigned narrow_attr_done = 0; // ... and the single-pass CSR kernel's forms
     // scratch, reused across calls
     twtml::DevBuf partials, shards, stat_partials, stat_shards, state, loss_hist, out10, tmp_a, tmp_b, gather, lower, upd_parts, slices, wprev;
     twtml::IngestLane lane[2];                 // [0] blocking ingest on the compute stream, [1] asynchronous ingest on the copy stream

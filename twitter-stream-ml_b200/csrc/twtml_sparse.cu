@@ -175,18 +175,27 @@ int csr_partial_width(const twtml_batch* b) { return (int)b->d + 2; }
 static int launch_narrow(twtml_ctx* ctx, const NarrowArgs& a, int mode, unsigned grid)
 {
     const size_t smem = narrow_smem_bytes(a.d, a.warps);
-#define TW_NARROW(MODE_)                                                                                  \
-    do {                                                                                                  \
-        auto kern = k_csr_narrow<MODE_>;                                                                  \
-        TW_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));     \
-        kern<<<grid, (a.warps + 1) * 32, smem, ctx->stream>>>(a);                                               \
+    static const bool no_pairs = getenv("TWTML_NO_PAIRS") != nullptr; // A/B switch: one row per warp for every width
+    const bool pairs = a.d <= kNarrowPairMaxD && !no_pairs;
+    const unsigned form = 1u << ((pairs ? 4 : 0) + mode);
+#define TW_NARROW(KERNEL_, MODE_)                                                                                \
+    do {                                                                                                         \
+        auto kern = KERNEL_<MODE_>;                                                                              \
+        if (!(ctx->narrow_attr_done & form)) { /* once per context (= per device) and kernel form */             \
+            TW_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));        \
+            ctx->narrow_attr_done |= form;                                                                       \
+        }                                                                                                        \
+        kern<<<grid, (a.warps + 1) * 32, smem, ctx->stream>>>(a);                                                \
     } while (0)
-    switch (mode) {
-    case MODE_TRAIN: TW_NARROW(MODE_TRAIN); break;
-    case MODE_TRAIN_STATS: TW_NARROW(MODE_TRAIN_STATS); break;
-    case MODE_PREDICT: TW_NARROW(MODE_PREDICT); break;
-    default: TW_NARROW(MODE_PREDICT_STATS); break;
+#define TW_NARROW_MODE(KERNEL_)                                          \
+    switch (mode) {                                                      \
+    case MODE_TRAIN: TW_NARROW(KERNEL_, MODE_TRAIN); break;              \
+    case MODE_TRAIN_STATS: TW_NARROW(KERNEL_, MODE_TRAIN_STATS); break;  \
+    case MODE_PREDICT: TW_NARROW(KERNEL_, MODE_PREDICT); break;          \
+    default: TW_NARROW(KERNEL_, MODE_PREDICT_STATS); break;              \
     }
+    if (pairs) { TW_NARROW_MODE(k_csr_narrow_pairs) } else { TW_NARROW_MODE(k_csr_narrow) }
+#undef TW_NARROW_MODE
 #undef TW_NARROW
     TW_CUDA(cudaGetLastError());
     return 0;
