@@ -350,6 +350,9 @@ class Bench:
         kern_ms_per_launch = self.max_over_ranks(kern_ms / max(kern_launches, 1))
         assert len(model.lastLossHistory) == iters, "iterations were skipped"
         value = world * n * iters * steps / (dev_ms * 1e-3)
+        import hashlib
+        w_now = np.ascontiguousarray(model.latestModel().weights.toArray())
+        weights_sha = hashlib.sha256(w_now.tobytes()).hexdigest()[:16]   # equal across N when the N ranks hold the same global batch
 
         # ---- end to end through the C ABI with HOST buffers: ingest (H2D) + stats + train + results (D2H)
         e2e = None
@@ -438,8 +441,8 @@ class Bench:
             resident_gb = (nnz * 12 * (1 if narrow else 2) + n * 24) / 1e9 if csr else n * (d + 2) * 8 / 1e9
             cfg = workload_config(name, dict(wl, rows=wl["rows"]), world)
             rec = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warmup,
-                   "ms_per_step": dev_ms / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                   "dtype": "f64", "data": "synthetic", "config": cfg,
+                   "ms_per_step": dev_ms / steps, "higher_is_better": True, "scaling": self.args.scaling, "vs_baseline": None,
+                   "dtype": "f64", "data": "synthetic", "config": cfg, "weights_sha256_16": weights_sha,
                    "notes": {"rows_trained_per_gpu": n,
                              **({"tweets_per_gpu": n_tweets, "nnz_per_gpu": nnz} if tweets is not None else {}),
                              "exchange": "one exchange of the shard partials per iteration",
@@ -484,6 +487,8 @@ def main():
     ap.add_argument("--e2e-sync", action="store_true", help="blocking ingest in the e2e leg (A/B against the pipelined default)")
     ap.add_argument("--no-numa-bind", action="store_true", help="do not move the process to the GPU's NUMA node before allocating host buffers")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="label of the line: 'strong' when --rows was set to total_rows / N so that the job's work is fixed")
     args = ap.parse_args()
     wl = dict(WORKLOADS[args.workload])
     if args.rows:
