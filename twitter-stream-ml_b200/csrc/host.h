@@ -81,6 +81,13 @@ struct twtml_ctx {
     std::atomic<int> live_handles{0}; // models + batches created on this context and not yet freed
     // peer-memory exchange of the shard vectors (reduce.cuh PeerExchange); falls back to NCCL when not set up
     bool p2p_ok = false;
+    bool peers_mappable = false;            // every rank can map every rank's memory (the dense scheme additionally needs world | 8)
+    // wide-model exchange buffer (reduce.cuh WideExchange), set up at the first training call that needs it
+    double* wxbuf = nullptr;
+    long long wx_dpad = 0;
+    double* wx_peer[twtml::kMaxShards] = {};
+    bool wx_ipc[twtml::kMaxShards] = {};
+    bool wx_failed = false;
     double* xbuf = nullptr;                 // this rank's exchange buffer
     double* peer[twtml::kMaxShards] = {};   // every rank's buffer as mapped here (peer[rank] == xbuf)
     bool peer_ipc[twtml::kMaxShards] = {};  // mapped with cudaIpcOpenMemHandle (to be closed)

@@ -313,6 +313,7 @@ struct SliceArgs {
     double* w;
     const TrainState* state;
     int W, slice_len, lo, hi;
+    int hi_all; // model width d
     int updater;
     double step, reg;
 };
@@ -347,6 +348,152 @@ static __global__ void __launch_bounds__(1024) k_update_slice(const SliceArgs a)
     }
 }
 
+// ---- the same over peer memory: all-to-all + sliced update + all-gather in ONE kernel -------------------------------
+// Every rank owns a wide exchange buffer, mapped by all ranks:  G[dpad] (its gradient vector, lossSum and count at
+// G[d], G[d + 1]) | WX[dpad] (the new weights, written by the ranks that own the columns) | flag_g[8] | flag_w[8] |
+// CTA counter | sequence number.  Per iteration, after the rank's column pass has left its gradient in G:
+//   k_wide_signal        tells every peer "my G of exchange seq is complete" (flag_g[me] on the peer := seq);
+//   k_update_slice_p2p   waits for all flag_g, then for each of ITS columns loads the W partial sums straight from the
+//                        peers' G over NVLink (plain peer loads, added in rank order), applies the updater and stores
+//                        the new weight into EVERY rank's WX (peer stores); its last CTA raises flag_w[me] everywhere;
+//   k_norms_wide_p2p     waits for all flag_w, moves WX into the model's weights and takes the convergence norms on the
+//                        way (old weight still in place: no copy of the previous weights is kept);
+//   k_slice_finish       as before; it also advances the buffer's sequence number.
+// No NCCL call, no staging copy; transfers are the 2 x (W-1)/W x 8 d bytes per rank that the all-to-all + all-gather
+// moved, but issued by the SMs that consume / produce them.  Reuse is safe without a second parity: a rank rewrites G
+// only after its k_norms_wide_p2p saw every flag_w (so every peer has finished reading G), and peers write WX(seq + 1)
+// only after this rank signalled G(seq + 1), which follows its own reading of WX(seq) in stream order.
+struct WideExchange {
+    double* peer[kMaxShards]; // base of rank r's wide exchange buffer, as mapped here
+    long long dpad;           // doubles per region
+    int world, rank;
+};
+__host__ __device__ __forceinline__ double* wx_G(double* base) { return base; }
+__host__ __device__ __forceinline__ double* wx_W(double* base, long long dpad) { return base + dpad; }
+__host__ __device__ __forceinline__ unsigned long long* wx_flag_g(double* base, long long dpad) { return reinterpret_cast<unsigned long long*>(base + 2 * dpad); }
+__host__ __device__ __forceinline__ unsigned long long* wx_flag_w(double* base, long long dpad) { return wx_flag_g(base, dpad) + kMaxShards; }
+__host__ __device__ __forceinline__ unsigned* wx_counter(double* base, long long dpad) { return reinterpret_cast<unsigned*>(wx_flag_g(base, dpad) + 2 * kMaxShards); }
+__host__ __device__ __forceinline__ unsigned long long* wx_seq(double* base, long long dpad) { return wx_flag_g(base, dpad) + 2 * kMaxShards + 1; }
+constexpr size_t wide_exchange_bytes(long long dpad) { return (size_t)(2 * dpad) * 8 + (2 * kMaxShards + 2) * 8 + 64; }
+
+__device__ __forceinline__ double ld_sys_f64(const double* p)
+{
+    double v;
+    asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// all `n` flags (written by other GPUs) have reached seq; false after ~10 s
+__device__ __forceinline__ bool wait_flags(const unsigned long long* flags, int n, unsigned long long seq)
+{
+    __shared__ int timed_out;
+    if (threadIdx.x == 0) timed_out = 0;
+    __syncthreads();
+    if (threadIdx.x < n) {
+        const volatile unsigned long long* f = flags + threadIdx.x;
+        const long long t0 = clock64();
+        while (*f < seq)
+            if (clock64() - t0 > 20000000000ll) { timed_out = 1; break; }
+        __threadfence_system();
+    }
+    __syncthreads();
+    __threadfence_system();
+    return timed_out == 0;
+}
+
+static __global__ void k_wide_signal(WideExchange wx, const TrainState* state)
+{
+    if (state->done || threadIdx.x != 0) return;
+    double* mine = wx.peer[wx.rank];
+    const unsigned long long seq = *wx_seq(mine, wx.dpad) + 1ull;
+    __threadfence_system(); // the column pass before this launch wrote G
+    for (int r = 0; r < wx.world; ++r) *reinterpret_cast<volatile unsigned long long*>(wx_flag_g(wx.peer[r], wx.dpad) + wx.rank) = seq;
+}
+
+static __global__ void __launch_bounds__(1024) k_update_slice_p2p(const SliceArgs a, WideExchange wx, TrainState* state, double* __restrict__ pairs_out)
+{
+    if (state->done) return;
+    double* mine = wx.peer[wx.rank];
+    const unsigned long long seq = *wx_seq(mine, wx.dpad) + 1ull;
+    if (!wait_flags(wx_flag_g(mine, wx.dpad), wx.world, seq)) {
+        if (threadIdx.x == 0) { state->done = 1; state->pad = kPeerTimeoutMark; }
+        return;
+    }
+    const int d = a.hi_all; // model width: (lossSum, count) sit behind it
+    double cnt = 0.0;
+    for (int r = 0; r < wx.world; ++r) cnt += ld_sys_f64(wx_G(wx.peer[r]) + d + 1);
+    if (blockIdx.x == 0 && threadIdx.x < 2 * wx.world) // the W (lossSum, count) pairs for k_slice_finish
+        pairs_out[threadIdx.x] = ld_sys_f64(wx_G(wx.peer[threadIdx.x >> 1]) + d + (threadIdx.x & 1));
+    if (cnt > 0.0) {
+        const double this_step = a.step / sqrt((double)state->iter);
+        const int j0 = a.lo + blockIdx.x * kWideCols, j1 = min(a.hi, j0 + kWideCols);
+        for (int j = j0 + threadIdx.x; j < j1; j += blockDim.x) {
+            double g = 0.0;
+            for (int r = 0; r < wx.world; ++r) g += ld_sys_f64(wx_G(wx.peer[r]) + j); // rank order
+            g = g / cnt;
+            const double wo = a.w[j];
+            double wn;
+            if (a.updater == 1) {
+                wn = __dmul_rn(wo, 1.0 - this_step * a.reg);
+                wn = __dadd_rn(wn, __dmul_rn(-this_step, g));
+            } else {
+                wn = __dadd_rn(wo, __dmul_rn(-this_step, g));
+                if (a.updater == 2) {
+                    const double shr = a.reg * this_step;
+                    const double m = fabs(wn) - shr;
+                    const double sg = (double)((wn > 0.0) - (wn < 0.0));
+                    wn = sg * (m > 0.0 ? m : 0.0);
+                }
+            }
+            for (int r = 0; r < wx.world; ++r) wx_W(wx.peer[r], wx.dpad)[j] = wn;
+        }
+    } else { // an empty sample: the weights stand
+        const int j0 = a.lo + blockIdx.x * kWideCols, j1 = min(a.hi, j0 + kWideCols);
+        for (int j = j0 + threadIdx.x; j < j1; j += blockDim.x) {
+            const double wo = a.w[j];
+            for (int r = 0; r < wx.world; ++r) wx_W(wx.peer[r], wx.dpad)[j] = wo;
+        }
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned* counter = wx_counter(mine, wx.dpad);
+        if (atomicAdd(counter, 1u) == gridDim.x - 1u) { // last CTA of this rank: its whole slice is on its way everywhere
+            *counter = 0u;
+            __threadfence_system();
+            for (int r = 0; r < wx.world; ++r) *reinterpret_cast<volatile unsigned long long*>(wx_flag_w(wx.peer[r], wx.dpad) + wx.rank) = seq;
+        }
+    }
+}
+
+// WX -> w with the three norms of the step on the way (per-CTA partials over kWideCols columns each, as k_norms_wide)
+static __global__ void __launch_bounds__(1024) k_norms_wide_p2p(double* __restrict__ w, WideExchange wx, int d, TrainState* state,
+                                                                 double* __restrict__ part)
+{
+    __shared__ double sm32[32];
+    if (state->done) return;
+    double* mine = wx.peer[wx.rank];
+    const unsigned long long seq = *wx_seq(mine, wx.dpad) + 1ull;
+    if (!wait_flags(wx_flag_w(mine, wx.dpad), wx.world, seq)) {
+        if (threadIdx.x == 0) { state->done = 1; state->pad = kPeerTimeoutMark; }
+        return;
+    }
+    const double* wxw = wx_W(mine, wx.dpad);
+    double dn2 = 0.0, wn2 = 0.0, l1 = 0.0;
+    const int lo = blockIdx.x * kWideCols, hi = min(d, lo + kWideCols);
+    for (int j = lo + threadIdx.x; j < hi; j += blockDim.x) {
+        const double wn = __ldcg(wxw + j), df = w[j] - wn; // written by other GPUs: read past L1
+        w[j] = wn;
+        dn2 += df * df;
+        wn2 += wn * wn;
+        l1 += fabs(wn);
+    }
+    dn2 = block_sum_1024(dn2, sm32);
+    wn2 = block_sum_1024(wn2, sm32);
+    l1 = block_sum_1024(l1, sm32);
+    if (threadIdx.x == 0) { part[blockIdx.x * 3] = dn2; part[blockIdx.x * 3 + 1] = wn2; part[blockIdx.x * 3 + 2] = l1; }
+}
+
 // per-CTA partials of ||w_prev - w||^2, ||w||^2, ||w||_1 over kWideCols columns each
 static __global__ void __launch_bounds__(1024) k_norms_wide(const double* __restrict__ w, const double* __restrict__ wprev, int d,
                                                      const TrainState* state, double* __restrict__ part)
@@ -368,10 +515,11 @@ static __global__ void __launch_bounds__(1024) k_norms_wide(const double* __rest
 }
 
 static __global__ void __launch_bounds__(1024) k_slice_finish(const UpdateArgs a, const double* __restrict__ pairs, int W,
-                                                       const double* __restrict__ part, int nparts)
+                                                       const double* __restrict__ part, int nparts, unsigned long long* seq_word = nullptr)
 {
     __shared__ double sm32[32];
     if (a.state->done) return;
+    if (seq_word && threadIdx.x == 0) *seq_word += 1ull; // the peer-memory exchange of this iteration is complete on this rank
     double loss = 0.0, cnt = 0.0;
     for (int r = 0; r < W; ++r) { loss += pairs[2 * r]; cnt += pairs[2 * r + 1]; }
     double dn2 = 0.0, wn2 = 0.0, l1 = 0.0;

@@ -189,21 +189,21 @@ struct PeerCard {
     int ok;
 };
 
-static int setup_peer_exchange(twtml_ctx* ctx)
+// Collective: every rank offers `mine` (cudaMalloc'ed; null = "I could not allocate") and ends up with all ranks'
+// buffers mapped in peer[] (CUDA IPC between processes, plain peer access between threads of one process), or with
+// *all_ok = 0 on every rank when any rank failed.
+static int map_peer_buffers(twtml_ctx* ctx, void* mine_ptr, double* peer[kMaxShards], bool ipc[kMaxShards], int* all_ok)
 {
-    ctx->p2p_ok = false;
     const int W = ctx->world;
-    if (W < 2 || W > kMaxShards || kMaxShards % W != 0) return 0;
     PeerCard mine{};
     mine.pid = (long long)getpid();
     mine.dev = ctx->device;
-    mine.ok = 1;
-    if (cudaMalloc(&ctx->xbuf, kXbufBytes) != cudaSuccess || cudaMemset(ctx->xbuf, 0, kXbufBytes) != cudaSuccess ||
-        cudaIpcGetMemHandle(&mine.handle, ctx->xbuf) != cudaSuccess) {
+    mine.ok = mine_ptr != nullptr;
+    if (mine_ptr && cudaIpcGetMemHandle(&mine.handle, mine_ptr) != cudaSuccess) {
         cudaGetLastError();
         mine.ok = 0;
     }
-    mine.ptr = (unsigned long long)ctx->xbuf;
+    mine.ptr = (unsigned long long)mine_ptr;
     TW_TRY(ctx->gather.reserve(sizeof(PeerCard) * (size_t)W));
     char* g = ctx->gather.as<char>();
     TW_CUDA(cudaMemcpyAsync(g + sizeof(PeerCard) * ctx->rank, &mine, sizeof(mine), cudaMemcpyHostToDevice, ctx->stream));
@@ -214,19 +214,19 @@ static int setup_peer_exchange(twtml_ctx* ctx)
     int ok = 1;
     for (int r = 0; r < W; ++r) ok &= cards[r].ok;
     for (int r = 0; r < W && ok; ++r) {
-        if (r == ctx->rank) { ctx->peer[r] = ctx->xbuf; continue; }
+        if (r == ctx->rank) { peer[r] = static_cast<double*>(mine_ptr); continue; }
         if (cards[r].pid == mine.pid) { // another thread of this process: plain peer access
             int can = 0;
             cudaDeviceCanAccessPeer(&can, ctx->device, cards[r].dev);
             cudaError_t e = can ? cudaDeviceEnablePeerAccess(cards[r].dev, 0) : cudaErrorInvalidDevice;
             if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); e = cudaSuccess; }
             if (e != cudaSuccess) { cudaGetLastError(); ok = 0; break; }
-            ctx->peer[r] = reinterpret_cast<double*>(cards[r].ptr);
+            peer[r] = reinterpret_cast<double*>(cards[r].ptr);
         } else {
             void* p = nullptr;
             if (cudaIpcOpenMemHandle(&p, cards[r].handle, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ok = 0; break; }
-            ctx->peer[r] = static_cast<double*>(p);
-            ctx->peer_ipc[r] = true;
+            peer[r] = static_cast<double*>(p);
+            ipc[r] = true;
         }
     }
     // second round: a rank that could not map a peer vetoes the scheme for everybody
@@ -237,7 +237,67 @@ static int setup_peer_exchange(twtml_ctx* ctx)
     TW_CUDA(cudaMemcpyAsync(oks.data(), flags, sizeof(int) * (size_t)W, cudaMemcpyDeviceToHost, ctx->stream));
     TW_CUDA(cudaStreamSynchronize(ctx->stream));
     for (int r = 0; r < W; ++r) ok &= oks[r];
-    ctx->p2p_ok = ok != 0 && getenv("TWTML_NO_P2P") == nullptr;
+    *all_ok = ok;
+    return 0;
+}
+
+static int setup_peer_exchange(twtml_ctx* ctx)
+{
+    ctx->p2p_ok = false;
+    const int W = ctx->world;
+    if (W < 2 || W > kMaxShards) return 0;
+    if (cudaMalloc(&ctx->xbuf, kXbufBytes) != cudaSuccess || cudaMemset(ctx->xbuf, 0, kXbufBytes) != cudaSuccess) {
+        cudaGetLastError();
+        if (ctx->xbuf) cudaFree(ctx->xbuf);
+        ctx->xbuf = nullptr;
+    }
+    int ok = 0;
+    TW_TRY(map_peer_buffers(ctx, ctx->xbuf, ctx->peer, ctx->peer_ipc, &ok));
+    ctx->peers_mappable = ok != 0;
+    ctx->p2p_ok = ok != 0 && kMaxShards % W == 0 && getenv("TWTML_NO_P2P") == nullptr;
+    return 0;
+}
+
+// The wide exchange buffer (reduce.cuh WideExchange) for models of up to d columns.  Collective: called by every rank at
+// the same point of a training call (the decision depends on the model width and on what earlier calls allocated, both
+// equal on all ranks).
+static int setup_wide_exchange(twtml_ctx* ctx, long long d)
+{
+    const long long want = (d + 2 + 15) & ~15ll;
+    if (ctx->wx_dpad >= want) return 0;
+    TW_CUDA(cudaStreamSynchronize(ctx->stream));
+    for (int r = 0; r < kMaxShards; ++r) {
+        if (ctx->wx_ipc[r] && ctx->wx_peer[r]) cudaIpcCloseMemHandle(ctx->wx_peer[r]);
+        ctx->wx_peer[r] = nullptr;
+        ctx->wx_ipc[r] = false;
+    }
+    // nobody frees a buffer a peer may still be reading: the last exchange on the old one ended before this point on every
+    // rank, and the handle exchange below is a barrier before anyone touches the new one
+    double* old = ctx->wxbuf;
+    ctx->wxbuf = nullptr;
+    ctx->wx_dpad = 0;
+    const size_t bytes = wide_exchange_bytes(want);
+    void* p = nullptr;
+    if (cudaMalloc(&p, bytes) != cudaSuccess || cudaMemset(p, 0, bytes) != cudaSuccess) {
+        cudaGetLastError();
+        if (p) cudaFree(p);
+        p = nullptr;
+    }
+    int ok = 0;
+    TW_TRY(map_peer_buffers(ctx, p, ctx->wx_peer, ctx->wx_ipc, &ok));
+    if (old) cudaFree(old);
+    if (!ok) {
+        for (int r = 0; r < kMaxShards; ++r) {
+            if (ctx->wx_ipc[r] && ctx->wx_peer[r]) cudaIpcCloseMemHandle(ctx->wx_peer[r]);
+            ctx->wx_peer[r] = nullptr;
+            ctx->wx_ipc[r] = false;
+        }
+        if (p) cudaFree(p);
+        ctx->wx_failed = true; // every rank saw the same verdict: all fall back to the NCCL form from here on
+        return 0;
+    }
+    ctx->wxbuf = static_cast<double*>(p);
+    ctx->wx_dpad = want;
     return 0;
 }
 
@@ -247,6 +307,10 @@ static void teardown_peer_exchange(twtml_ctx* ctx)
         if (ctx->peer_ipc[r] && ctx->peer[r]) cudaIpcCloseMemHandle(ctx->peer[r]);
     if (ctx->xbuf) cudaFree(ctx->xbuf);
     ctx->xbuf = nullptr;
+    for (int r = 0; r < kMaxShards; ++r)
+        if (ctx->wx_ipc[r] && ctx->wx_peer[r]) cudaIpcCloseMemHandle(ctx->wx_peer[r]);
+    if (ctx->wxbuf) cudaFree(ctx->wxbuf);
+    ctx->wxbuf = nullptr;
 }
 
 int ctx_global_rows(twtml_ctx* ctx, int64_t n_local, int64_t* n_global, int64_t* row0)
@@ -526,6 +590,51 @@ static bool use_sliced(const twtml_ctx* ctx, const twtml_model* m, const twtml_b
     return ctx->world > 1 && b->csr && m->d > 2 * kWideCols && getenv("TWTML_NO_SLICED") == nullptr;
 }
 
+static bool use_sliced_p2p(const twtml_ctx* ctx, const twtml_model* m, const twtml_batch* b)
+{
+    static const bool off = getenv("TWTML_NO_P2P") != nullptr || getenv("TWTML_NO_P2P_WIDE") != nullptr;
+    return use_sliced(ctx, m, b) && ctx->peers_mappable && !ctx->wx_failed && !off;
+}
+
+static WideExchange wide_exchange(const twtml_ctx* ctx)
+{
+    WideExchange wx{};
+    for (int r = 0; r < ctx->world; ++r) wx.peer[r] = ctx->wx_peer[r];
+    wx.dpad = ctx->wx_dpad;
+    wx.world = ctx->world;
+    wx.rank = ctx->rank;
+    return wx;
+}
+
+// the peer-memory form of sliced_update (reduce.cuh): this rank's gradient already sits in its exchange buffer
+static int sliced_update_p2p(twtml_ctx* ctx, twtml_model* m, const twtml_batch* b, const UpdateArgs& ua)
+{
+    (void)b;
+    const int W = ctx->world, d = (int)m->d, slice_len = (d + W - 1) / W;
+    const WideExchange wx = wide_exchange(ctx);
+    double* pairs = ctx->slices.as<double>();
+    SliceArgs sa{};
+    sa.w = m->d_w;
+    sa.state = ua.state;
+    sa.W = W;
+    sa.slice_len = slice_len;
+    sa.lo = std::min(d, ctx->rank * slice_len);
+    sa.hi = std::min(d, sa.lo + slice_len);
+    sa.hi_all = d;
+    sa.updater = ua.updater;
+    sa.step = ua.step;
+    sa.reg = ua.reg;
+    const int nb = std::max(1, (sa.hi - sa.lo + kWideCols - 1) / kWideCols);
+    const int nparts = (d + kWideCols - 1) / kWideCols;
+    k_wide_signal<<<1, 32, 0, ctx->stream>>>(wx, ua.state);
+    k_update_slice_p2p<<<nb, 1024, 0, ctx->stream>>>(sa, wx, ua.state, pairs);
+    k_norms_wide_p2p<<<nparts, 1024, 0, ctx->stream>>>(m->d_w, wx, d, ua.state, ctx->upd_parts.as<double>());
+    k_slice_finish<<<1, 1024, 0, ctx->stream>>>(ua, pairs, W, ctx->upd_parts.as<double>(), nparts, wx_seq(ctx->wxbuf, ctx->wx_dpad));
+    TW_CUDA(cudaGetLastError());
+    ctx->prof.other_launches += 4;
+    return 0;
+}
+
 static int sliced_update(twtml_ctx* ctx, twtml_model* m, const twtml_batch* b, const UpdateArgs& ua)
 {
     const int W = ctx->world, d = (int)m->d, slice_len = (d + W - 1) / W;
@@ -553,6 +662,7 @@ static int sliced_update(twtml_ctx* ctx, twtml_model* m, const twtml_batch* b, c
     sa.slice_len = slice_len;
     sa.lo = std::min(d, ctx->rank * slice_len);
     sa.hi = std::min(d, sa.lo + slice_len);
+    sa.hi_all = d;
     sa.updater = ua.updater;
     sa.step = ua.step;
     sa.reg = ua.reg;
@@ -580,12 +690,13 @@ static int exchange_shards(twtml_ctx* ctx, const twtml_batch* b)
     return allgather_inplace(ctx, ctx->shards.as<double>(), (size_t)b->plan.spr * partial_width(b), ncclDouble, sizeof(double));
 }
 
-static int reduce_local(twtml_ctx* ctx, const twtml_batch* b, bool gated)
+static int reduce_local(twtml_ctx* ctx, const twtml_batch* b, bool gated, bool wide_p2p = false)
 {
     const int pv = partial_width(b), spr = b->plan.spr;
     const TrainState* gate = gated ? ctx->state.as<TrainState>() : nullptr;
     double* mine = ctx->shards.as<double>() + (size_t)ctx->rank * spr * pv;
     if (b->csr) {
+        if (wide_p2p) mine = wx_G(ctx->wxbuf); // the peers read the gradient where the column pass leaves it
         TW_TRY(csr_reduce(ctx, b, mine, gate));
     } else if (gated && use_p2p(ctx, b)) {
         PeerExchange px{};
@@ -773,6 +884,11 @@ static int do_train(twtml_model* m, const twtml_batch* b, bool with_stats, doubl
     const bool may_stop_early = ctx->world == 1 && ctx->host_done_dev != nullptr;
     if (may_stop_early) { *ctx->host_done = 0; ua.host_done = ctx->host_done_dev; }
 
+    bool wide_p2p = false;
+    if (use_sliced_p2p(ctx, m, b)) { // collective decision + (first time, or a wider model) the buffer's set-up
+        TW_TRY(setup_wide_exchange(ctx, m->d));
+        wide_p2p = !ctx->wx_failed && ctx->wxbuf != nullptr;
+    }
     const bool prof = ctx->profiling;
     size_t ne = 0;
     if (prof) TW_CUDA(cudaEventRecord(prof_event(ctx, ne++), ctx->stream));
@@ -786,10 +902,10 @@ static int do_train(twtml_model* m, const twtml_batch* b, bool with_stats, doubl
         // dense: the timed "iteration kernel" is k_dense_iter alone; CSR: row pass + column pass + fold
         if (prof && !b->csr) TW_CUDA(cudaEventRecord(prof_event(ctx, ne++), ctx->stream));
         ctx->prof.iter_launches += 1;
-        TW_TRY(reduce_local(ctx, b, true));
+        TW_TRY(reduce_local(ctx, b, true, wide_p2p));
         if (prof && b->csr) TW_CUDA(cudaEventRecord(prof_event(ctx, ne++), ctx->stream));
         if (use_sliced(ctx, m, b)) {
-            TW_TRY(sliced_update(ctx, m, b, ua));
+            TW_TRY(wide_p2p ? sliced_update_p2p(ctx, m, b, ua) : sliced_update(ctx, m, b, ua));
             if (i == 1 && with_stats) TW_TRY(reduce_stats(ctx, b));
             continue;
         }
