@@ -33,15 +33,20 @@ namespace twtml {
 constexpr int kNarrowMaxD = 2048;
 constexpr int kNarrowMaxWarps = 16;                   // consumer warps (one more warp produces: 544 threads)
 constexpr int kNarrowThreadsMax = (kNarrowMaxWarps + 1) * 32;
-constexpr int kNarrowK = 3;                           // entries per lane kept in registers between the two halves
+#ifndef TWTML_NARROW_K
+#define TWTML_NARROW_K 3
+#endif
+constexpr int kNarrowK = TWTML_NARROW_K;              // entries per lane kept in registers between the two halves
 constexpr int kNarrowTileLog = 10;
 constexpr int kNarrowTile = 1 << kNarrowTileLog;      // entries per tile
-constexpr int kNarrowStages = 4;                      // (kNarrowStages - 1) * kNarrowTile >= kNarrowMaxD + kNarrowTile - 1
+constexpr int kNarrowStages = 4;                      // default ring depth: (stages - 1) * kNarrowTile >= kNarrowMaxD + kNarrowTile - 1
+constexpr int kNarrowStagesMax = 8;                   // the deeper ring (more bytes in flight per SM, two accumulators fewer)
 constexpr int kNarrowRing = kNarrowStages * kNarrowTile;
 constexpr int kNarrowSlack = 8;                       // colidx / vals carry a few entries past the last one (copies are 16-byte wide)
 constexpr long long kNarrowRowCost = 96;              // a row's fixed work costs about as much as this many entries
 constexpr int kNarrowRedDoubles = kNarrowMaxWarps * (2 + kStatStride);
 constexpr size_t kNarrowRingBytes = 128 + (size_t)kNarrowRing * 12; // barriers | values | column indices
+__host__ __device__ constexpr size_t narrow_ring_bytes(int stages) { return 128 + (size_t)stages * kNarrowTile * 12; }
 
 struct NarrowArgs {
     const long long* rowptr; // n + 1
@@ -63,17 +68,17 @@ struct NarrowArgs {
 };
 
 // consumer warps per CTA: as many private accumulators as shared memory holds beside the ring and the weights
-__host__ __device__ inline int narrow_warps(int d)
+__host__ __device__ inline int narrow_warps(int d, int stages = kNarrowStages)
 {
-    const long long room = 227ll * 1024 - (long long)kNarrowRingBytes - 8ll * d - 8ll * kNarrowRedDoubles - 256;
+    const long long room = 227ll * 1024 - (long long)narrow_ring_bytes(stages) - 8ll * d - 8ll * kNarrowRedDoubles - 256;
     const long long w = room / (8ll * (d > 0 ? d : 1));
     return (int)(w > kNarrowMaxWarps ? kNarrowMaxWarps : w);
 }
 // resident CTAs of the single-pass kernel per SM (the grid at ingest is sized to this)
 __host__ __device__ inline int narrow_ctas_per_sm(int d) { (void)d; return 1; }
-__host__ __device__ inline size_t narrow_smem_bytes(int d, int warps)
+__host__ __device__ inline size_t narrow_smem_bytes(int d, int warps, int stages = kNarrowStages)
 {
-    return kNarrowRingBytes + (size_t)8 * d + 8 * kNarrowRedDoubles + (size_t)8 * d * warps;
+    return narrow_ring_bytes(stages) + (size_t)8 * d + 8 * kNarrowRedDoubles + (size_t)8 * d * warps;
 }
 
 __device__ __forceinline__ uint32_t keep_u32(uint32_t x)
@@ -165,9 +170,11 @@ __device__ __forceinline__ void narrow_warp_stat(Stat7& s)
     }
 }
 
-template <int MODE>
+template <int MODE, int STAGES = kNarrowStages>
 __global__ void __launch_bounds__(kNarrowThreadsMax, 1) k_csr_narrow(const NarrowArgs a)
 {
+    constexpr int kNarrowStages = STAGES, kNarrowRing = STAGES * kNarrowTile; // this instance's ring (shadow the defaults)
+    constexpr size_t kNarrowRingBytes = narrow_ring_bytes(STAGES);
     constexpr bool kTrain = (MODE == MODE_TRAIN || MODE == MODE_TRAIN_STATS);
     constexpr bool kStats = (MODE == MODE_TRAIN_STATS || MODE == MODE_PREDICT_STATS);
     constexpr bool kPerRow = kStats || MODE == MODE_PREDICT; // something is written per row
@@ -378,9 +385,11 @@ __global__ void __launch_bounds__(kNarrowThreadsMax, 1) k_csr_narrow(const Narro
 constexpr int kNarrowPairMaxD = 1024;
 constexpr int kPairK = 5; // 16-lane slots of a row kept in registers between the two halves (80 entries)
 
-template <int MODE>
+template <int MODE, int STAGES = kNarrowStages>
 __global__ void __launch_bounds__(kNarrowThreadsMax, 1) k_csr_narrow_pairs(const NarrowArgs a)
 {
+    constexpr int kNarrowStages = STAGES, kNarrowRing = STAGES * kNarrowTile; // this instance's ring (shadow the defaults)
+    constexpr size_t kNarrowRingBytes = narrow_ring_bytes(STAGES);
     constexpr bool kTrain = (MODE == MODE_TRAIN || MODE == MODE_TRAIN_STATS);
     constexpr bool kStats = (MODE == MODE_TRAIN_STATS || MODE == MODE_PREDICT_STATS);
     constexpr bool kPerRow = kStats || MODE == MODE_PREDICT;

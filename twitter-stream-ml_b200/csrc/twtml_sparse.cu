@@ -41,6 +41,11 @@ static int exclusive_sum(IngestLane& lane, const long long* in, long long* out, 
 
 static unsigned blocks_for(long long n, int threads) { return (unsigned)std::max<long long>(1, (n + threads - 1) / threads); }
 
+// A/B switches of the single-pass kernel (read once): TWTML_NARROW_PAIRS=1 row pairs (d <= 1024), TWTML_NARROW_STAGES=8 the
+// deeper entry ring.  Both change the launch shape fixed at ingest (warps per CTA), hence they are process-wide.
+static bool narrow_pairs_on() { static const bool on = getenv("TWTML_NARROW_PAIRS") != nullptr; return on; }
+static int narrow_stages() { static const int st = (getenv("TWTML_NARROW_STAGES") && atoi(getenv("TWTML_NARROW_STAGES")) == 8) ? 8 : kNarrowStages; return st; }
+
 // Narrow models: no transpose at all, only the first row of every CTA of the single-pass kernel.
 // Returns 1 when the batch does not qualify (the caller then builds the global transpose).
 static int csr_finalize_narrow(twtml_ctx* ctx, IngestLane& lane, twtml_batch* b)
@@ -48,7 +53,7 @@ static int csr_finalize_narrow(twtml_ctx* ctx, IngestLane& lane, twtml_batch* b)
     const long long n = b->n;
     const int d = (int)b->d;
     if (d > kNarrowMaxD || getenv("TWTML_NO_NARROW")) return 1; // a function of the model width only: every rank decides alike
-    const int warps = narrow_warps(d);
+    const int warps = narrow_warps(d, narrow_stages());
     if (warps < 4) return 1;
     // one partial vector per CTA of a grid fixed here: the plan's "blocks" are those CTAs
     const long long grid = std::max<long long>(1, std::min<long long>((n + warps - 1) / warps, (long long)ctx->sm_count * narrow_ctas_per_sm(d)));
@@ -174,27 +179,31 @@ int csr_partial_width(const twtml_batch* b) { return (int)b->d + 2; }
 
 static int launch_narrow(twtml_ctx* ctx, const NarrowArgs& a, int mode, unsigned grid)
 {
-    const size_t smem = narrow_smem_bytes(a.d, a.warps);
-    static const bool no_pairs = getenv("TWTML_NO_PAIRS") != nullptr; // A/B switch: one row per warp for every width
-    const bool pairs = a.d <= kNarrowPairMaxD && !no_pairs;
-    const unsigned form = 1u << ((pairs ? 4 : 0) + mode);
-#define TW_NARROW(KERNEL_, MODE_)                                                                                \
+    const int stages = narrow_stages();
+    const size_t smem = narrow_smem_bytes(a.d, a.warps, stages);
+    const bool pairs = a.d <= kNarrowPairMaxD && narrow_pairs_on();
+    const unsigned form = 1u << ((pairs ? 4 : 0) + (stages == 8 ? 8 : 0) + mode);
+#define TW_NARROW(KERNEL_, MODE_, ST_)                                                                           \
     do {                                                                                                         \
-        auto kern = KERNEL_<MODE_>;                                                                              \
+        auto kern = KERNEL_<MODE_, ST_>;                                                                         \
         if (!(ctx->narrow_attr_done & form)) { /* once per context (= per device) and kernel form */             \
             TW_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));        \
             ctx->narrow_attr_done |= form;                                                                       \
         }                                                                                                        \
         kern<<<grid, (a.warps + 1) * 32, smem, ctx->stream>>>(a);                                                \
     } while (0)
-#define TW_NARROW_MODE(KERNEL_)                                          \
-    switch (mode) {                                                      \
-    case MODE_TRAIN: TW_NARROW(KERNEL_, MODE_TRAIN); break;              \
-    case MODE_TRAIN_STATS: TW_NARROW(KERNEL_, MODE_TRAIN_STATS); break;  \
-    case MODE_PREDICT: TW_NARROW(KERNEL_, MODE_PREDICT); break;          \
-    default: TW_NARROW(KERNEL_, MODE_PREDICT_STATS); break;              \
+#define TW_NARROW_MODE(KERNEL_, ST_)                                          \
+    switch (mode) {                                                           \
+    case MODE_TRAIN: TW_NARROW(KERNEL_, MODE_TRAIN, ST_); break;              \
+    case MODE_TRAIN_STATS: TW_NARROW(KERNEL_, MODE_TRAIN_STATS, ST_); break;  \
+    case MODE_PREDICT: TW_NARROW(KERNEL_, MODE_PREDICT, ST_); break;          \
+    default: TW_NARROW(KERNEL_, MODE_PREDICT_STATS, ST_); break;              \
     }
-    if (pairs) { TW_NARROW_MODE(k_csr_narrow_pairs) } else { TW_NARROW_MODE(k_csr_narrow) }
+    if (stages == 8) {
+        if (pairs) { TW_NARROW_MODE(k_csr_narrow_pairs, 8) } else { TW_NARROW_MODE(k_csr_narrow, 8) }
+    } else {
+        if (pairs) { TW_NARROW_MODE(k_csr_narrow_pairs, kNarrowStages) } else { TW_NARROW_MODE(k_csr_narrow, kNarrowStages) }
+    }
 #undef TW_NARROW_MODE
 #undef TW_NARROW
     TW_CUDA(cudaGetLastError());
@@ -368,14 +377,34 @@ struct TweetArgs {
 // knows its row count (rdd.count, LinearRegression.scala:59) at once; also refuses texts the featuriser cannot hold
 static int tweets_precheck(const TweetArgs& t, int64_t* n_kept)
 {
-    int64_t kept = 0;
-    for (int64_t i = 0; i < t.n; ++i) {
-        const int64_t len = t.text_off[i + 1] - t.text_off[i];
-        if (len < 0) return fail(TWTML_E_INVALID_ARG, "twtml_batch_from_tweets: text offsets decrease at tweet %lld", (long long)i);
-        if (len > kMaxTerms + 1) return fail(TWTML_E_INVALID_ARG, "a tweet has %lld UTF-16 units; the featuriser takes at most %d", (long long)len, kMaxTerms + 1);
-        kept += t.is_retweet[i] != 0 && t.retweet_cnt[i] >= t.rt_begin && t.retweet_cnt[i] <= t.rt_end;
+    const int nt = (int)std::max<int64_t>(1, std::min<int64_t>(std::min(16u, std::max(1u, std::thread::hardware_concurrency())), t.n / 65536));
+    std::vector<int64_t> kept((size_t)nt, 0), bad((size_t)nt, -1);
+    auto scan = [&](int k) { // a slice of the tweets on its own host thread
+        const int64_t lo = t.n * k / nt, hi = t.n * (k + 1) / nt;
+        int64_t c = 0;
+        for (int64_t i = lo; i < hi; ++i) {
+            const int64_t len = t.text_off[i + 1] - t.text_off[i];
+            if ((len < 0 || len > kMaxTerms + 1) && bad[(size_t)k] < 0) bad[(size_t)k] = i;
+            c += t.is_retweet[i] != 0 && t.retweet_cnt[i] >= t.rt_begin && t.retweet_cnt[i] <= t.rt_end;
+        }
+        kept[(size_t)k] = c;
+    };
+    if (nt == 1) scan(0);
+    else {
+        std::vector<std::thread> th;
+        for (int k = 0; k < nt; ++k) th.emplace_back(scan, k);
+        for (auto& x : th) x.join();
     }
-    *n_kept = kept;
+    int64_t total = 0;
+    for (int k = 0; k < nt; ++k) {
+        if (bad[(size_t)k] >= 0) {
+            const int64_t i = bad[(size_t)k], len = t.text_off[i + 1] - t.text_off[i];
+            if (len < 0) return fail(TWTML_E_INVALID_ARG, "twtml_batch_from_tweets: text offsets decrease at tweet %lld", (long long)i);
+            return fail(TWTML_E_INVALID_ARG, "a tweet has %lld UTF-16 units; the featuriser takes at most %d", (long long)len, kMaxTerms + 1);
+        }
+        total += kept[(size_t)k];
+    }
+    *n_kept = total;
     return 0;
 }
 
