@@ -571,7 +571,7 @@ static int reserve_scratch(twtml_ctx* ctx, const twtml_model* m, const twtml_bat
     TW_TRY(ctx->shards.reserve(sizeof(double) * (size_t)kMaxShards * std::max(1, ctx->world) * pv));
     TW_TRY(ctx->stat_partials.reserve(sizeof(double) * (size_t)std::max<long long>(1, b->plan.nblocks) * kStatStride));
     TW_TRY(ctx->stat_shards.reserve(sizeof(double) * (size_t)kMaxShards * std::max(1, ctx->world) * kStatStride));
-    TW_TRY(ctx->state.reserve(sizeof(TrainState)));
+    TW_TRY(ctx->state.reserve(sizeof(TrainState) + 64)); // + the CTA counter of k_shard_reduce_update
     TW_TRY(ctx->loss_hist.reserve(sizeof(double) * (size_t)std::max(1, m->num_iter)));
     TW_TRY(ctx->out10.reserve(sizeof(double) * 16));
     TW_TRY(ctx->upd_parts.reserve(sizeof(double) * 3 * (size_t)((m->d + kWideCols - 1) / kWideCols)));
@@ -858,6 +858,8 @@ static int do_train(twtml_model* m, const twtml_batch* b, bool with_stats, doubl
     if (with_stats && out_real) { TW_TRY(ctx->tmp_b.reserve(sizeof(double) * (size_t)std::max<int64_t>(1, b->n))); dr = ctx->tmp_b.as<double>(); }
 
     TrainState* st = ctx->state.as<TrainState>();
+    unsigned* fuse_counter = reinterpret_cast<unsigned*>(ctx->state.as<char>() + sizeof(TrainState));
+    TW_CUDA(cudaMemsetAsync(fuse_counter, 0, sizeof(unsigned), ctx->stream));
     k_train_init<<<1, 1024, 0, ctx->stream>>>(st, m->d_w, (int)m->d, m->updater, m->reg, m->num_iter);
     TW_CUDA(cudaGetLastError());
     if (with_stats && m->num_iter < 1) { // no iteration to ride on
@@ -889,6 +891,8 @@ static int do_train(twtml_model* m, const twtml_batch* b, bool with_stats, doubl
         TW_TRY(setup_wide_exchange(ctx, m->d));
         wide_p2p = !ctx->wx_failed && ctx->wxbuf != nullptr;
     }
+    static const bool no_fuse = getenv("TWTML_NO_FUSED_TAIL") != nullptr; // A/B switch
+    const bool fused_tail = ctx->world == 1 && !no_fuse && m->d <= 2 * kWideCols && (!b->csr || b->narrow);
     const bool prof = ctx->profiling;
     size_t ne = 0;
     if (prof) TW_CUDA(cudaEventRecord(prof_event(ctx, ne++), ctx->stream));
@@ -899,11 +903,21 @@ static int do_train(twtml_model* m, const twtml_batch* b, bool with_stats, doubl
         const int mode = (i == 1 && with_stats) ? MODE_TRAIN_STATS : MODE_TRAIN;
         if (prof) TW_CUDA(cudaEventRecord(prof_event(ctx, ne++), ctx->stream));
         TW_TRY(run_pass(ctx, m, b, mode, dp, dr, 0));
-        // dense: the timed "iteration kernel" is k_dense_iter alone; CSR: row pass + column pass + fold
-        if (prof && !b->csr) TW_CUDA(cudaEventRecord(prof_event(ctx, ne++), ctx->stream));
+        // the timed "iteration kernel": k_dense_iter / k_csr_narrow alone; wide CSR: row pass + column pass + fold
+        const bool one_kernel = !b->csr || b->narrow;
+        if (prof && one_kernel) TW_CUDA(cudaEventRecord(prof_event(ctx, ne++), ctx->stream));
         ctx->prof.iter_launches += 1;
+        if (fused_tail) { // one GPU, narrow model: shard reduce + update in one launch
+            const int spr = b->plan.spr;
+            dim3 grid((pv + 31) / 32, spr);
+            k_shard_reduce_update<<<grid, 1024, 0, ctx->stream>>>(ctx->partials.as<double>(), pv, b->plan, ctx->shards.as<double>(), fuse_counter, ua);
+            TW_CUDA(cudaGetLastError());
+            ctx->prof.other_launches += 1;
+            if (i == 1 && with_stats) TW_TRY(reduce_stats(ctx, b));
+            continue;
+        }
         TW_TRY(reduce_local(ctx, b, true, wide_p2p));
-        if (prof && b->csr) TW_CUDA(cudaEventRecord(prof_event(ctx, ne++), ctx->stream));
+        if (prof && !one_kernel) TW_CUDA(cudaEventRecord(prof_event(ctx, ne++), ctx->stream));
         if (use_sliced(ctx, m, b)) {
             TW_TRY(wide_p2p ? sliced_update_p2p(ctx, m, b, ua) : sliced_update(ctx, m, b, ua));
             if (i == 1 && with_stats) TW_TRY(reduce_stats(ctx, b));

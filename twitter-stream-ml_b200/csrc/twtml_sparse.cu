@@ -44,6 +44,7 @@ static unsigned blocks_for(long long n, int threads) { return (unsigned)std::max
 // A/B switches of the single-pass kernel (read once): TWTML_NARROW_PAIRS=1 row pairs (d <= 1024), TWTML_NARROW_STAGES=8 the
 // deeper entry ring.  Both change the launch shape fixed at ingest (warps per CTA), hence they are process-wide.
 static bool narrow_pairs_on() { static const bool on = getenv("TWTML_NARROW_PAIRS") != nullptr; return on; }
+static bool narrow_rows2_on() { static const bool on = getenv("TWTML_NARROW_ROWS2") != nullptr; return on; }
 static int narrow_stages() { static const int st = (getenv("TWTML_NARROW_STAGES") && atoi(getenv("TWTML_NARROW_STAGES")) == 8) ? 8 : kNarrowStages; return st; }
 
 // Narrow models: no transpose at all, only the first row of every CTA of the single-pass kernel.
@@ -53,7 +54,8 @@ static int csr_finalize_narrow(twtml_ctx* ctx, IngestLane& lane, twtml_batch* b)
     const long long n = b->n;
     const int d = (int)b->d;
     if (d > kNarrowMaxD || getenv("TWTML_NO_NARROW")) return 1; // a function of the model width only: every rank decides alike
-    const int warps = narrow_warps(d, narrow_stages());
+    int warps = narrow_warps(d, narrow_stages());
+    if (narrow_rows2_on()) warps = std::min(warps, kNarrow2MaxWarps);
     if (warps < 4) return 1;
     // one partial vector per CTA of a grid fixed here: the plan's "blocks" are those CTAs
     const long long grid = std::max<long long>(1, std::min<long long>((n + warps - 1) / warps, (long long)ctx->sm_count * narrow_ctas_per_sm(d)));
@@ -182,7 +184,8 @@ static int launch_narrow(twtml_ctx* ctx, const NarrowArgs& a, int mode, unsigned
     const int stages = narrow_stages();
     const size_t smem = narrow_smem_bytes(a.d, a.warps, stages);
     const bool pairs = a.d <= kNarrowPairMaxD && narrow_pairs_on();
-    const unsigned form = 1u << ((pairs ? 4 : 0) + (stages == 8 ? 8 : 0) + mode);
+    const bool rows2 = !pairs && narrow_rows2_on();
+    const unsigned form = 1u << ((pairs ? 4 : 0) + (stages == 8 ? 8 : 0) + (rows2 ? 16 : 0) + mode);
 #define TW_NARROW(KERNEL_, MODE_, ST_)                                                                           \
     do {                                                                                                         \
         auto kern = KERNEL_<MODE_, ST_>;                                                                         \
@@ -200,9 +203,9 @@ static int launch_narrow(twtml_ctx* ctx, const NarrowArgs& a, int mode, unsigned
     default: TW_NARROW(KERNEL_, MODE_PREDICT_STATS, ST_); break;              \
     }
     if (stages == 8) {
-        if (pairs) { TW_NARROW_MODE(k_csr_narrow_pairs, 8) } else { TW_NARROW_MODE(k_csr_narrow, 8) }
+        if (pairs) { TW_NARROW_MODE(k_csr_narrow_pairs, 8) } else if (rows2) { TW_NARROW_MODE(k_csr_narrow2, 8) } else { TW_NARROW_MODE(k_csr_narrow, 8) }
     } else {
-        if (pairs) { TW_NARROW_MODE(k_csr_narrow_pairs, kNarrowStages) } else { TW_NARROW_MODE(k_csr_narrow, kNarrowStages) }
+        if (pairs) { TW_NARROW_MODE(k_csr_narrow_pairs, kNarrowStages) } else if (rows2) { TW_NARROW_MODE(k_csr_narrow2, kNarrowStages) } else { TW_NARROW_MODE(k_csr_narrow, kNarrowStages) }
     }
 #undef TW_NARROW_MODE
 #undef TW_NARROW
