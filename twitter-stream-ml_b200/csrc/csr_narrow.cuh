@@ -851,6 +851,81 @@ __global__ void __launch_bounds__(kNarrowThreadsMax, 1) k_csr_narrow_pairs(const
     }
 }
 
+// ---- ingest: the order of a row's entries inside the copy the single-pass kernel streams -----------------------------
+// The kernel's shared-memory traffic, not HBM, is its busiest unit (profiles/r02_ncu_csr_narrow_*.csv: the LSU data pipe is
+// 63-66 % busy and 40 % of its wavefronts are bank conflicts).  The conflicts come from the gathers of w[col] and the
+// read-modify-writes of g[col]: 8-byte accesses of a half-warp are conflict-free only if its 16 columns fall into 16
+// different 8-byte banks, i.e. differ mod 16, and the columns of 16 consecutive entries of a row are as good as random.
+// But a row's entries may be visited in ANY order (no column occurs twice in a row), so ingest lays them out for the
+// kernel: sort the row by (col mod 16) -- keeping column order inside a class -- and deal that sequence round robin over
+// the row's 16-entry half-slots.  Entries of one class then sit in different half-slots (as long as the class has no
+// more entries than the row has half-slots), and each half-warp access touches (nearly) 16 different banks.
+// The batch keeps the caller's order as well: export, the two-pass kernels and the checks read that one.
+static __global__ void __launch_bounds__(256) k_narrow_permute(const long long* __restrict__ rowptr, long long n, const int* __restrict__ colidx,
+                                                                const double* __restrict__ vals, int* __restrict__ pcol, double* __restrict__ pval)
+{
+    __shared__ int cnt[8][16];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const unsigned lt = (1u << lane) - 1u;
+    const long long nw = (long long)gridDim.x * 8;
+    for (long long r = (long long)blockIdx.x * 8 + wib; r < n; r += nw) {
+        const long long kb = rowptr[r];
+        const int m = (int)(rowptr[r + 1] - kb);
+        if (m <= 16) { // a single half-slot: nothing to arrange
+            if (lane < m) { pcol[kb + lane] = colidx[kb + lane]; pval[kb + lane] = vals[kb + lane]; }
+            continue;
+        }
+        if (lane < 16) cnt[wib][lane] = 0;
+        __syncwarp();
+        for (int b = 0; b < m; b += 32) { // entries per class
+            const int e = b + lane;
+            const bool in = e < m;
+            const int cls = in ? (colidx[kb + e] & 15) : 16 + lane; // lanes past the row's end: keys of their own
+            const unsigned peers = __match_any_sync(0xffffffffu, cls);
+            if (in && (peers & lt) == 0u) cnt[wib][cls] += __popc(peers); // the group's lowest lane counts for it
+            __syncwarp();
+        }
+        const int tot = lane < 16 ? cnt[wib][lane] : 0;
+        int incl = tot;
+#pragma unroll
+        for (int dl = 1; dl < 16; dl <<= 1) {
+            const int up = __shfl_up_sync(0xffffffffu, incl, dl);
+            if (lane >= dl) incl += up;
+        }
+        __syncwarp();
+        if (lane < 16) cnt[wib][lane] = incl - tot; // where the class's next entry goes in the class-sorted sequence
+        __syncwarp();
+        const int H = (m + 15) >> 4, rr = m - 16 * (H - 1); // half-slots; entries of the last one
+        for (int b = 0; b < m; b += 32) {
+            const int e = b + lane;
+            const bool in = e < m;
+            const int c = in ? colidx[kb + e] : 0;
+            const int cls = in ? (c & 15) : 16 + lane;
+            const unsigned peers = __match_any_sync(0xffffffffu, cls);
+            const int within = __popc(peers & lt);
+            const int k = in ? cnt[wib][cls] + within : 0;
+            __syncwarp();
+            if (in && within == 0) cnt[wib][cls] += __popc(peers);
+            __syncwarp();
+            if (in) { // position k of the sorted sequence -> (half-slot, place): places below rr exist in all H half-slots
+                int hs, tpl;
+                if (k < rr * H) {
+                    tpl = k / H;
+                    hs = k - tpl * H;
+                } else {
+                    const int k2 = k - rr * H, q2 = k2 / (H - 1);
+                    tpl = rr + q2;
+                    hs = k2 - q2 * (H - 1);
+                }
+                const long long dst = kb + hs * 16 + tpl;
+                pcol[dst] = c;
+                pval[dst] = vals[kb + e];
+            }
+        }
+        __syncwarp();
+    }
+}
+
 // ---- ingest: first row of every CTA, balancing entries + kNarrowRowCost per row (a row's fixed work -- bounds, butterfly,
 // bookkeeping -- costs about as much as that many entries)
 static __global__ void k_narrow_bounds(const long long* __restrict__ rowptr, long long n, long long G, long long* __restrict__ bounds)

@@ -160,6 +160,8 @@ struct twtml_batch {
     bool narrow = false;
     int nwarps = 0;
     long long* bounds = nullptr;
+    int* pcolidx = nullptr;        // the entries in the order the single-pass kernel streams them (k_narrow_permute), or null
+    double* pvals = nullptr;
     double* diff = nullptr;        // residuals of the current iteration, n
     twtml::Plan plan{};
 };

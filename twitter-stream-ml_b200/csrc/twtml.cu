@@ -984,7 +984,7 @@ void batch_free_locked(twtml_batch* b)
     cudaStreamSynchronize(b->ctx->stream);
     for (void* p : {(void*)b->X, (void*)b->rowptr, (void*)b->colidx, (void*)b->vals, (void*)b->labels, (void*)b->colptr, (void*)b->rowidx,
                     (void*)b->cvals, (void*)b->headbits, (void*)b->nzcol, (void*)b->win_first_nz, (void*)b->wkey, (void*)b->win_first_part,
-                    (void*)b->win_last_part, (void*)b->diff, (void*)b->bounds})
+                    (void*)b->win_last_part, (void*)b->diff, (void*)b->bounds, (void*)b->pcolidx, (void*)b->pvals})
         pool_free(b->ctx, p);
     b->ctx->live_handles -= 1;
     delete b;

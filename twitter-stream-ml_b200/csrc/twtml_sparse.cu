@@ -62,6 +62,14 @@ static int csr_finalize_narrow(twtml_ctx* ctx, IngestLane& lane, twtml_batch* b)
     TW_TRY(dev_alloc(ctx, lane, &b->bounds, (size_t)grid + 1));
     k_narrow_bounds<<<blocks_for(grid + 1, 256), 256, 0, lane.stream>>>(b->rowptr, n, grid, b->bounds);
     TW_CUDA(cudaGetLastError());
+    static const bool no_permute = getenv("TWTML_NO_NARROW_PERMUTE") != nullptr; // A/B switch
+    if (!no_permute && b->nnz > 0) { // the kernel's own copy of the entries, laid out against shared-memory bank conflicts
+        TW_TRY(dev_alloc(ctx, lane, &b->pcolidx, (size_t)b->nnz + kNarrowSlack));
+        TW_TRY(dev_alloc(ctx, lane, &b->pvals, (size_t)b->nnz + kNarrowSlack));
+        const unsigned pg = (unsigned)std::min<long long>((n + 7) / 8, (long long)ctx->sm_count * 16);
+        k_narrow_permute<<<std::max(1u, pg), 256, 0, lane.stream>>>(b->rowptr, n, b->colidx, b->vals, b->pcolidx, b->pvals);
+        TW_CUDA(cudaGetLastError());
+    }
     b->narrow = true;
     b->nwarps = warps;
     memset(&b->plan, 0, sizeof(b->plan));
@@ -219,8 +227,8 @@ int csr_launch_iter(twtml_ctx* ctx, const twtml_model* m, const twtml_batch* b, 
     if (b->narrow) {
         NarrowArgs na{};
         na.rowptr = b->rowptr;
-        na.colidx = b->colidx;
-        na.vals = b->vals;
+        na.colidx = b->pcolidx ? b->pcolidx : b->colidx;
+        na.vals = b->pvals ? b->pvals : b->vals;
         na.labels = b->labels;
         na.w = m->d_w;
         na.state = ctx->state.as<TrainState>();
