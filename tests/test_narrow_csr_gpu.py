@@ -72,11 +72,11 @@ SHAPES = {
     "all_empty": (64, 40, lambda rng, r: 0, 1e-2),
     "tweet_like_d1004": (60000, 1004, lambda rng, r: rng.integers(5, 144), 5e-4),
     "d1": (1000, 1, lambda rng, r: rng.integers(0, 2), 1e-2),
-    # widths the row-pair kernel serves (d <= 1024: two adjacent rows per warp, one per half-warp)
-    "pairs_max_rows_d1024": (301, 1024, lambda rng, r: 1024, 2e-4),            # every pair spans three tiles; odd row count
-    "pairs_long_and_empty_d1024": (999, 1024, lambda rng, r: (0, 1024, 3, 700, 0, 0, 81)[r % 7], 2e-4),
-    "pairs_tail_loop_d200": (5001, 200, lambda rng, r: rng.integers(70, 201), 1e-3),   # > 80 entries: beyond the lanes' registers
-    "pairs_three_rows": (3, 1004, lambda rng, r: (100, 0, 17)[r], 1e-3),
+    # more ring / tail shapes at d <= 1024
+    "max_rows_d1024": (301, 1024, lambda rng, r: 1024, 2e-4),            # rows of a whole tile; odd row count
+    "long_and_empty_d1024": (999, 1024, lambda rng, r: (0, 1024, 3, 700, 0, 0, 81)[r % 7], 2e-4),
+    "tail_loop_d200": (5001, 200, lambda rng, r: rng.integers(70, 201), 1e-3),   # rows around and beyond the 96 entries the lanes keep in registers
+    "three_rows": (3, 1004, lambda rng, r: (100, 0, 17)[r], 1e-3),
 }
 
 

@@ -11,7 +11,7 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-SO_PATH = os.environ.get("TWTML_LIB") or os.path.join(HERE, "libtwtml.so")   # TWTML_LIB: an experimental build (tools/)
+SO_PATH = os.path.join(HERE, "libtwtml.so")
 HEADER = os.path.join(os.path.dirname(HERE), "include", "twtml.h")
 SOURCES = ["twtml.cu", "twtml_sparse.cu", "twtml_noalloc.cu", "twtml_group.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

@@ -33,20 +33,15 @@ namespace twtml {
 constexpr int kNarrowMaxD = 2048;
 constexpr int kNarrowMaxWarps = 16;                   // consumer warps (one more warp produces: 544 threads)
 constexpr int kNarrowThreadsMax = (kNarrowMaxWarps + 1) * 32;
-#ifndef TWTML_NARROW_K
-#define TWTML_NARROW_K 3
-#endif
-constexpr int kNarrowK = TWTML_NARROW_K;              // entries per lane kept in registers between the two halves
+constexpr int kNarrowK = 3;                           // entries per lane kept in registers between the two halves
 constexpr int kNarrowTileLog = 10;
 constexpr int kNarrowTile = 1 << kNarrowTileLog;      // entries per tile
-constexpr int kNarrowStages = 4;                      // default ring depth: (stages - 1) * kNarrowTile >= kNarrowMaxD + kNarrowTile - 1
-constexpr int kNarrowStagesMax = 8;                   // the deeper ring (more bytes in flight per SM, two accumulators fewer)
+constexpr int kNarrowStages = 4;                      // (kNarrowStages - 1) * kNarrowTile >= kNarrowMaxD + kNarrowTile - 1
 constexpr int kNarrowRing = kNarrowStages * kNarrowTile;
 constexpr int kNarrowSlack = 8;                       // colidx / vals carry a few entries past the last one (copies are 16-byte wide)
 constexpr long long kNarrowRowCost = 96;              // a row's fixed work costs about as much as this many entries
 constexpr int kNarrowRedDoubles = kNarrowMaxWarps * (2 + kStatStride);
 constexpr size_t kNarrowRingBytes = 128 + (size_t)kNarrowRing * 12; // barriers | values | column indices
-__host__ __device__ constexpr size_t narrow_ring_bytes(int stages) { return 128 + (size_t)stages * kNarrowTile * 12; }
 
 struct NarrowArgs {
     const long long* rowptr; // n + 1
@@ -68,17 +63,15 @@ struct NarrowArgs {
 };
 
 // consumer warps per CTA: as many private accumulators as shared memory holds beside the ring and the weights
-__host__ __device__ inline int narrow_warps(int d, int stages = kNarrowStages)
+__host__ __device__ inline int narrow_warps(int d)
 {
-    const long long room = 227ll * 1024 - (long long)narrow_ring_bytes(stages) - 8ll * d - 8ll * kNarrowRedDoubles - 256;
+    const long long room = 227ll * 1024 - (long long)kNarrowRingBytes - 8ll * d - 8ll * kNarrowRedDoubles - 256;
     const long long w = room / (8ll * (d > 0 ? d : 1));
     return (int)(w > kNarrowMaxWarps ? kNarrowMaxWarps : w);
 }
-// resident CTAs of the single-pass kernel per SM (the grid at ingest is sized to this)
-__host__ __device__ inline int narrow_ctas_per_sm(int d) { (void)d; return 1; }
-__host__ __device__ inline size_t narrow_smem_bytes(int d, int warps, int stages = kNarrowStages)
+__host__ __device__ inline size_t narrow_smem_bytes(int d, int warps)
 {
-    return narrow_ring_bytes(stages) + (size_t)8 * d + 8 * kNarrowRedDoubles + (size_t)8 * d * warps;
+    return kNarrowRingBytes + (size_t)8 * d + 8 * kNarrowRedDoubles + (size_t)8 * d * warps;
 }
 
 __device__ __forceinline__ uint32_t keep_u32(uint32_t x)
@@ -170,11 +163,9 @@ __device__ __forceinline__ void narrow_warp_stat(Stat7& s)
     }
 }
 
-template <int MODE, int STAGES = kNarrowStages>
+template <int MODE>
 __global__ void __launch_bounds__(kNarrowThreadsMax, 1) k_csr_narrow(const NarrowArgs a)
 {
-    constexpr int kNarrowStages = STAGES, kNarrowRing = STAGES * kNarrowTile; // this instance's ring (shadow the defaults)
-    constexpr size_t kNarrowRingBytes = narrow_ring_bytes(STAGES);
     constexpr bool kTrain = (MODE == MODE_TRAIN || MODE == MODE_TRAIN_STATS);
     constexpr bool kStats = (MODE == MODE_TRAIN_STATS || MODE == MODE_PREDICT_STATS);
     constexpr bool kPerRow = kStats || MODE == MODE_PREDICT; // something is written per row
@@ -367,484 +358,6 @@ __global__ void __launch_bounds__(kNarrowThreadsMax, 1) k_csr_narrow(const Narro
                 Stat7 s;
                 stat_load(s, sst + q * kStatStride);
                 stat_merge(tot, s);
-            }
-            stat_store(a.stat_partials + (long long)blockIdx.x * kStatStride, tot);
-        }
-    }
-}
-
-// ---- two rows of a warp in flight ---------------------------------------------------------------------------------
-// k_csr_narrow is latency-bound: ~190 instructions per row, mostly one dependent chain (entry loads -> weight gathers ->
-// fma -> five shuffle steps -> residual -> accumulator read-modify-writes), with four warps per scheduler to hide it
-// (profiles/r02_ncu_csr_narrow_source.csv: stall samples spread evenly over the chain, issue slots and the shared-memory
-// pipe both half busy).  This form gives every warp instruction-level parallelism instead of more warps: it takes its
-// rows two at a time (local rows j and j + 1, sixteen rows apart in the batch) through ONE basic block, so the two rows'
-// gathers, dot products and butterflies interleave in the schedule; only the accumulator updates stay in row order
-// (row j's, then row j + 1's), which keeps every column's sum the fixed sequence it was: results are bit-identical to
-// k_csr_narrow.  Two rows are taken together only when both fit the ring beside what the warp still holds.
-constexpr int kNarrow2MaxWarps = 15; // + the producer warp = 512 threads: 128 registers per thread for two rows' worth of state
-template <int MODE, int STAGES = kNarrowStages>
-__global__ void __launch_bounds__((kNarrow2MaxWarps + 1) * 32, 1) k_csr_narrow2(const NarrowArgs a)
-{
-    constexpr int kNarrowStages = STAGES, kNarrowRing = STAGES * kNarrowTile;
-    constexpr size_t kNarrowRingBytes = narrow_ring_bytes(STAGES);
-    constexpr bool kTrain = (MODE == MODE_TRAIN || MODE == MODE_TRAIN_STATS);
-    constexpr bool kStats = (MODE == MODE_TRAIN_STATS || MODE == MODE_PREDICT_STATS);
-    constexpr bool kPerRow = kStats || MODE == MODE_PREDICT;
-    constexpr unsigned kMask = kNarrowRing - 1;
-    if (kTrain && a.state->done) return;
-
-    extern __shared__ __align__(128) unsigned char smem[];
-    uint64_t* full = reinterpret_cast<uint64_t*>(smem);
-    uint64_t* empty = full + kNarrowStages;
-    double* val_ring = reinterpret_cast<double*>(smem + 128);
-    int* col_ring = reinterpret_cast<int*>(smem + 128 + (size_t)kNarrowRing * 8);
-    double* w_s = reinterpret_cast<double*>(smem + kNarrowRingBytes);
-    double* sred = w_s + a.d;
-    double* gacc = sred + kNarrowRedDoubles;
-    const int t = threadIdx.x, lane = t & 31, warp = t >> 5, W = a.warps, d = a.d;
-    const unsigned long long iter_seed =
-        splitmix64((unsigned long long)(42 + (a.iter_override > 0 ? a.iter_override : (kTrain ? a.state->iter : 0))));
-    const bool sampling = kTrain && a.frac < 1.0;
-
-    const long long C0 = a.bounds[blockIdx.x], C1 = a.bounds[blockIdx.x + 1];
-    const int E0 = (int)a.rowptr[C0], E1 = (int)a.rowptr[C1], Ea = E0 & ~3;
-    const int ntiles = E1 > E0 ? (E1 - Ea + kNarrowTile - 1) >> kNarrowTileLog : 0;
-    const uint64_t policy = l2_evict_first_policy();
-    auto fill = [&](int tl) { // producer lane only
-        const int s = tl & (kNarrowStages - 1);
-        const int start = Ea + tl * kNarrowTile;
-        const int cnt = min(kNarrowTile, (E1 - start + 3) & ~3);
-        mbar_expect_tx(&full[s], (uint32_t)cnt * 12u);
-        tma_load_1d(val_ring + s * kNarrowTile, a.vals + start, (uint32_t)cnt * 8u, &full[s], policy);
-        tma_load_1d(col_ring + s * kNarrowTile, a.colidx + start, (uint32_t)cnt * 4u, &full[s], policy);
-    };
-    if (t == W * 32) {
-        for (int s = 0; s < kNarrowStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], (uint32_t)W); }
-        mbar_fence_init();
-        for (int tl = 0; tl < min(ntiles, kNarrowStages); ++tl) fill(tl);
-    }
-    for (int j = t; j < d; j += blockDim.x) w_s[j] = a.w[j];
-    if (kTrain)
-        for (int j = t; j < W * d; j += blockDim.x) gacc[j] = 0.0;
-    __syncthreads();
-
-    double my_loss = 0.0, my_cnt = 0.0, keep_acc = 0.0, keep_y = 0.0;
-    Stat7 my_stat;
-    stat_zero(my_stat);
-
-    if (warp == W) {
-        if (lane == 0) {
-            for (int tl = kNarrowStages; tl < ntiles; ++tl) {
-                mbar_wait(&empty[tl & (kNarrowStages - 1)], (uint32_t)((tl / kNarrowStages - 1) & 1));
-                fill(tl);
-            }
-        }
-    } else {
-        const int span = (int)(C1 - C0);
-        const int R1 = span > warp ? (span - warp + W - 1) / W : 0;
-        auto rowof = [&](int j) { return C0 + (warp + W * j); };
-        const uint32_t ws = keep_u32(smem_u32(w_s)), gs = keep_u32(smem_u32(gacc + (size_t)warp * d)), vs = keep_u32(smem_u32(val_ring)),
-                       cs = keep_u32(smem_u32(col_ring)), fb = keep_u32(smem_u32(full)), eb = keep_u32(smem_u32(empty));
-        unsigned waited = 0, released = 0;
-        auto wait_tile = [&]() {
-            mbar_wait_addr(fb + 8u * (waited & (kNarrowStages - 1)), (waited / kNarrowStages) & 1u);
-            ++waited;
-        };
-        auto release_tile = [&]() { // only a tile that was observed full
-            if (waited <= released) wait_tile();
-            if (lane == 0) mbar_arrive_addr(eb + 8u * (released & (kNarrowStages - 1)));
-            ++released;
-        };
-        int lo1 = 0, hi1 = 0, lo2, hi2;
-        double y1 = 0.0, y2;
-        auto load_chunk = [&](int b0, int& lo, int& hi, double& y) {
-            const int j0 = b0 + lane;
-            const bool in = j0 < R1;
-            const long long row = in ? rowof(j0) : C0;
-            lo = (int)a.rowptr[in ? row : C1];
-            hi = (int)a.rowptr[in ? row + 1 : C1];
-            y = a.labels[row];
-        };
-        struct Row {
-            int kb, ne;
-            double y, acc;
-            int c[kNarrowK];
-            double v[kNarrowK];
-        };
-        // the dot product of one row (entries already in the ring): slots in registers, the rest straight from the ring
-        auto row_dot = [&](Row& r) {
-            const unsigned o0 = (unsigned)(r.kb - Ea + lane);
-            r.acc = 0.0;
-#pragma unroll
-            for (int i = 0; i < kNarrowK; ++i) {
-                const unsigned idx = (o0 + 32u * i) & kMask;
-                r.c[i] = 0;
-                r.v[i] = 0.0;
-                narrow_slot_dot(lane + 32 * i < r.ne, cs + 4u * idx, vs + 8u * idx, ws, r.c[i], r.v[i], r.acc);
-            }
-        };
-        auto row_dot_tail = [&](Row& r) { // entries beyond the register slots (rows of more than 32 kNarrowK entries)
-#pragma unroll 1
-            for (int k = lane + 32 * kNarrowK; k < r.ne; k += 32) {
-                const unsigned idx = (unsigned)(r.kb - Ea + k) & kMask;
-                r.acc = fma(lds_f64(vs + 8u * idx), lds_f64(ws + 8u * (unsigned)lds_s32(cs + 4u * idx)), r.acc);
-            }
-        };
-        // everything after the butterfly for one row: residual, loss, accumulator updates, per-row outputs
-        auto row_finish = [&](Row& r, int j) {
-            const int sel = j & 31;
-            if (kTrain) {
-                const bool keep = !sampling || row_sampled(iter_seed, a.row0_global + (unsigned long long)rowof(j), a.frac);
-                if (keep) {
-                    const double diff = r.acc - r.y;
-                    my_loss += diff * diff / 2.0;
-                    my_cnt += 1.0;
-#pragma unroll
-                    for (int i = 0; i < kNarrowK; ++i) narrow_slot_add(lane + 32 * i < r.ne, r.c[i], r.v[i], diff, gs);
-#pragma unroll 1
-                    for (int k = lane + 32 * kNarrowK; k < r.ne; k += 32) {
-                        const unsigned idx = (unsigned)(r.kb - Ea + k) & kMask;
-                        const uint32_t ga = gs + 8u * (unsigned)lds_s32(cs + 4u * idx);
-                        sts_f64(ga, fma(diff, lds_f64(vs + 8u * idx), lds_f64(ga)));
-                    }
-                    __syncwarp(); // the next row's lanes may meet these columns
-                }
-            }
-            if (kPerRow) {
-                if (lane == sel) { keep_acc = r.acc; keep_y = r.y; }
-                if (sel == 31 || j == R1 - 1) {
-                    if (lane <= sel) {
-                        const long long row = rowof(j - sel + lane);
-                        if (kStats) {
-                            const double pr = round_half_up(keep_acc + 0.0);
-                            stat_add(my_stat, keep_y, pr);
-                            if (a.out_pred) a.out_pred[row] = pr;
-                            if (a.out_real) a.out_real[row] = keep_y;
-                        } else {
-                            a.out_pred[row] = keep_acc + 0.0;
-                        }
-                    }
-                }
-            }
-        };
-        if (R1 > 0) load_chunk(0, lo2, hi2, y2);
-        int j = 0;
-        while (j < R1) {
-            const int sel = j & 31;
-            if (sel == 0) {
-                lo1 = lo2;
-                hi1 = hi2;
-                y1 = y2;
-                if (j + 32 < R1) load_chunk(j + 32, lo2, hi2, y2);
-            }
-            Row ra, rb;
-            ra.kb = __shfl_sync(0xffffffffu, lo1, sel);
-            const int kea = __shfl_sync(0xffffffffu, hi1, sel);
-            ra.y = __shfl_sync(0xffffffffu, y1, sel);
-            ra.ne = kea - ra.kb;
-            // the row after it in this warp's list, when it sits in the same chunk of bounds
-            const bool have_b = sel < 31 && j + 1 < R1;
-            const int selb = have_b ? sel + 1 : sel;
-            rb.kb = __shfl_sync(0xffffffffu, lo1, selb);
-            const int keb = __shfl_sync(0xffffffffu, hi1, selb);
-            rb.y = __shfl_sync(0xffffffffu, y1, selb);
-            rb.ne = keb - rb.kb;
-            if (ra.ne > 0) {
-                const unsigned tb = (unsigned)(ra.kb - Ea) >> kNarrowTileLog, te = (unsigned)(kea - 1 - Ea) >> kNarrowTileLog;
-#pragma unroll 1
-                while (released < tb) release_tile();
-#pragma unroll 1
-                while (waited <= te) wait_tile();
-            }
-            // Row b rides along if its last tile can be resident beside the tiles this warp has not given back yet (the
-            // producer refills slot t - STAGES only after every warp gave tile t - STAGES back: waiting for more would wait
-            // on ourselves)
-            bool two = have_b;
-            if (two && rb.ne > 0) {
-                const unsigned teb = (unsigned)(keb - 1 - Ea) >> kNarrowTileLog;
-                two = teb < released + (unsigned)kNarrowStages;
-                if (two) {
-#pragma unroll 1
-                    while (waited <= teb) wait_tile();
-                }
-            }
-            if (two) {
-                row_dot(ra); // the two rows' register slots in one basic block: their loads interleave
-                row_dot(rb);
-                row_dot_tail(ra);
-                row_dot_tail(rb);
-#pragma unroll
-                for (int mk = 16; mk >= 1; mk >>= 1) {
-                    ra.acc += shfl_xor_f64(ra.acc, mk);
-                    rb.acc += shfl_xor_f64(rb.acc, mk);
-                }
-                row_finish(ra, j);
-                row_finish(rb, j + 1);
-                j += 2;
-            } else {
-                row_dot(ra);
-                row_dot_tail(ra);
-#pragma unroll
-                for (int mk = 16; mk >= 1; mk >>= 1) ra.acc += shfl_xor_f64(ra.acc, mk);
-                row_finish(ra, j);
-                j += 1;
-            }
-        }
-#pragma unroll 1
-        while (released < (unsigned)ntiles) release_tile();
-    }
-    __syncthreads();
-
-    if (kTrain) {
-        double* out = a.partials + (long long)blockIdx.x * (d + 2);
-        for (int j = t; j < d; j += blockDim.x) {
-            double s = gacc[j];
-            for (int q = 1; q < W; ++q) s += gacc[(size_t)q * d + j];
-            out[j] = s;
-        }
-        if (lane == 0 && warp < W) { sred[2 * warp] = my_loss; sred[2 * warp + 1] = my_cnt; }
-        __syncthreads();
-        if (t == 0) {
-            double ls = 0.0, cn = 0.0;
-            for (int q = 0; q < W; ++q) { ls += sred[2 * q]; cn += sred[2 * q + 1]; }
-            out[d] = ls;
-            out[d + 1] = cn;
-        }
-    }
-    if (kStats) {
-        double* sst = sred + 2 * kNarrowMaxWarps;
-        narrow_warp_stat(my_stat);
-        if (lane == 0 && warp < W) stat_store(sst + warp * kStatStride, my_stat);
-        __syncthreads();
-        if (t == 0) {
-            Stat7 tot;
-            stat_zero(tot);
-            for (int q = 0; q < W; ++q) {
-                Stat7 s2;
-                stat_load(s2, sst + q * kStatStride);
-                stat_merge(tot, s2);
-            }
-            stat_store(a.stat_partials + (long long)blockIdx.x * kStatStride, tot);
-        }
-    }
-}
-
-// ---- rows in pairs: models of at most kNarrowPairMaxD columns ------------------------------------------------
-// The row loop above is bound by its own length, not by memory: ~190 instructions and ~2000 cycles per row and warp,
-// one row at a time (profiles/r01_SUMMARY.md).  Here a warp takes two ADJACENT rows at once, one per half-warp: the
-// same instruction stream serves both rows (half the instructions per row), 16-lane slots waste fewer lanes on rows
-// of ~70 entries (80 lane slots instead of 96), the butterfly has four steps, and twice as many rows are in flight
-// per SM with the same sixteen accumulators.  The two rows of a pair share their warp's accumulator, so the second
-// half of the work runs in two rounds -- row A's lanes add diff_A * x_A, then row B's lanes add diff_B * x_B -- which
-// also keeps the per-column order of additions fixed (row order), hence bit-reproducible.  A pair of rows of at
-// most kNarrowPairMaxD entries each spans at most three tiles, which is what the four-tile ring allows.
-constexpr int kNarrowPairMaxD = 1024;
-constexpr int kPairK = 5; // 16-lane slots of a row kept in registers between the two halves (80 entries)
-
-template <int MODE, int STAGES = kNarrowStages>
-__global__ void __launch_bounds__(kNarrowThreadsMax, 1) k_csr_narrow_pairs(const NarrowArgs a)
-{
-    constexpr int kNarrowStages = STAGES, kNarrowRing = STAGES * kNarrowTile; // this instance's ring (shadow the defaults)
-    constexpr size_t kNarrowRingBytes = narrow_ring_bytes(STAGES);
-    constexpr bool kTrain = (MODE == MODE_TRAIN || MODE == MODE_TRAIN_STATS);
-    constexpr bool kStats = (MODE == MODE_TRAIN_STATS || MODE == MODE_PREDICT_STATS);
-    constexpr bool kPerRow = kStats || MODE == MODE_PREDICT;
-    constexpr unsigned kMask = kNarrowRing - 1;
-    if (kTrain && a.state->done) return;
-
-    extern __shared__ __align__(128) unsigned char smem[];
-    uint64_t* full = reinterpret_cast<uint64_t*>(smem);
-    uint64_t* empty = full + kNarrowStages;
-    double* val_ring = reinterpret_cast<double*>(smem + 128);
-    int* col_ring = reinterpret_cast<int*>(smem + 128 + (size_t)kNarrowRing * 8);
-    double* w_s = reinterpret_cast<double*>(smem + kNarrowRingBytes);
-    double* sred = w_s + a.d;
-    double* gacc = sred + kNarrowRedDoubles;
-    const int t = threadIdx.x, lane = t & 31, warp = t >> 5, W = a.warps, d = a.d;
-    const int half = lane >> 4, q = lane & 15;
-    const unsigned long long iter_seed =
-        splitmix64((unsigned long long)(42 + (a.iter_override > 0 ? a.iter_override : (kTrain ? a.state->iter : 0))));
-    const bool sampling = kTrain && a.frac < 1.0;
-
-    const long long C0 = a.bounds[blockIdx.x], C1 = a.bounds[blockIdx.x + 1];
-    const int E0 = (int)a.rowptr[C0], E1 = (int)a.rowptr[C1], Ea = E0 & ~3;
-    const int ntiles = E1 > E0 ? (E1 - Ea + kNarrowTile - 1) >> kNarrowTileLog : 0;
-    const uint64_t policy = l2_evict_first_policy();
-    auto fill = [&](int tl) { // producer lane only
-        const int s = tl & (kNarrowStages - 1);
-        const int start = Ea + tl * kNarrowTile;
-        const int cnt = min(kNarrowTile, (E1 - start + 3) & ~3);
-        mbar_expect_tx(&full[s], (uint32_t)cnt * 12u);
-        tma_load_1d(val_ring + s * kNarrowTile, a.vals + start, (uint32_t)cnt * 8u, &full[s], policy);
-        tma_load_1d(col_ring + s * kNarrowTile, a.colidx + start, (uint32_t)cnt * 4u, &full[s], policy);
-    };
-    if (t == W * 32) {
-        for (int s = 0; s < kNarrowStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], (uint32_t)W); }
-        mbar_fence_init();
-        for (int tl = 0; tl < min(ntiles, kNarrowStages); ++tl) fill(tl);
-    }
-    for (int j = t; j < d; j += blockDim.x) w_s[j] = a.w[j];
-    if (kTrain)
-        for (int j = t; j < W * d; j += blockDim.x) gacc[j] = 0.0;
-    __syncthreads();
-
-    double my_loss = 0.0, my_cnt = 0.0;
-    Stat7 my_stat;
-    stat_zero(my_stat);
-
-    if (warp == W) {
-        if (lane == 0) {
-            for (int tl = kNarrowStages; tl < ntiles; ++tl) {
-                mbar_wait(&empty[tl & (kNarrowStages - 1)], (uint32_t)((tl / kNarrowStages - 1) & 1));
-                fill(tl);
-            }
-        }
-    } else {
-        // warp w takes the CTA's row pairs w, w + W, ...: local pair j is rows C0 + 2 (w + W j) and the one after it
-        const int span = (int)(C1 - C0), npairs = (span + 1) >> 1;
-        const int P1 = npairs > warp ? (npairs - warp + W - 1) / W : 0;
-        auto pairrow = [&](int j) { return C0 + 2ll * (warp + W * j); };
-        const uint32_t ws = keep_u32(smem_u32(w_s)), gs = keep_u32(smem_u32(gacc + (size_t)warp * d)), vs = keep_u32(smem_u32(val_ring)),
-                       cs = keep_u32(smem_u32(col_ring)), fb = keep_u32(smem_u32(full)), eb = keep_u32(smem_u32(empty));
-        unsigned waited = 0, released = 0;
-        auto wait_tile = [&]() {
-            mbar_wait_addr(fb + 8u * (waited & (kNarrowStages - 1)), (waited / kNarrowStages) & 1u);
-            ++waited;
-        };
-        auto release_tile = [&]() { // only a tile that was observed full
-            if (waited <= released) wait_tile();
-            if (lane == 0) mbar_arrive_addr(eb + 8u * (released & (kNarrowStages - 1)));
-            ++released;
-        };
-        // Row pointers and labels of 16 pairs at a time: lane (16 h + i) holds those of row h of pair 16 c + i, for the
-        // current chunk c and the next one; a half-warp fetches its row's by one shuffle each.
-        int lo1 = 0, hi1 = 0, lo2 = 0, hi2 = 0;
-        double y1 = 0.0, y2 = 0.0;
-        auto load_chunk = [&](int b0, int& lo, int& hi, double& y) {
-            const int j0 = b0 + q;
-            const long long row = pairrow(j0 < P1 ? j0 : 0) + half;
-            const bool in = j0 < P1 && row < C1; // the last pair of an odd range has no second row: empty, at the stretch's end
-            lo = (int)a.rowptr[in ? row : C1];
-            hi = (int)a.rowptr[in ? row + 1 : C1];
-            y = a.labels[in ? row : C0];
-        };
-        if (P1 > 0) load_chunk(0, lo2, hi2, y2);
-        for (int j = 0; j < P1; ++j) {
-            const int sel = j & 15;
-            if (sel == 0) {
-                lo1 = lo2;
-                hi1 = hi2;
-                y1 = y2;
-                if (j + 16 < P1) load_chunk(j + 16, lo2, hi2, y2);
-            }
-            const int src = (lane & 16) | sel;
-            const int kb = __shfl_sync(0xffffffffu, lo1, src), ke = __shfl_sync(0xffffffffu, hi1, src);
-            const double y = __shfl_sync(0xffffffffu, y1, src);
-            const int pkb = __shfl_sync(0xffffffffu, lo1, sel), pke = __shfl_sync(0xffffffffu, hi1, 16 | sel); // the pair's stretch
-            const int ne = ke - kb;
-            const long long row = pairrow(j) + half;
-            const bool valid = row < C1;
-            if (pke > pkb) {
-                const unsigned tb = (unsigned)(pkb - Ea) >> kNarrowTileLog, te = (unsigned)(pke - 1 - Ea) >> kNarrowTileLog;
-#pragma unroll 1
-                while (released < tb) release_tile();
-#pragma unroll 1
-                while (waited <= te) wait_tile();
-            }
-            // w . x of both rows: 16-lane slots, the first kPairK of them stay in registers for the second half
-            const unsigned o0 = (unsigned)(kb - Ea + q);
-            int c[kPairK];
-            double v[kPairK];
-            double acc = 0.0;
-#pragma unroll
-            for (int i = 0; i < kPairK; ++i) {
-                const unsigned idx = (o0 + 16u * i) & kMask;
-                c[i] = 0;
-                v[i] = 0.0;
-                narrow_slot_dot(q + 16 * i < ne, cs + 4u * idx, vs + 8u * idx, ws, c[i], v[i], acc);
-            }
-            const int ne_max = max(ne, __shfl_xor_sync(0xffffffffu, ne, 16)); // both halves run the tail loops together
-#pragma unroll 1
-            for (int k = q + 16 * kPairK; k < ne_max; k += 16) {
-                if (k < ne) {
-                    const unsigned idx = (unsigned)(kb - Ea + k) & kMask;
-                    acc = fma(lds_f64(vs + 8u * idx), lds_f64(ws + 8u * (unsigned)lds_s32(cs + 4u * idx)), acc);
-                }
-            }
-#pragma unroll
-            for (int mk = 8; mk >= 1; mk >>= 1) acc += shfl_xor_f64(acc, mk); // inside the half-warp: the same bits in its 16 lanes
-            if (kTrain) {
-                const bool live = valid && (!sampling || row_sampled(iter_seed, a.row0_global + (unsigned long long)row, a.frac));
-                const double diff = acc - y;
-                if (live) {
-                    my_loss += diff * diff / 2.0;
-                    my_cnt += 1.0;
-                }
-#pragma unroll 1
-                for (int rnd = 0; rnd < 2; ++rnd) { // row A's additions, then row B's: they may meet on a column
-                    const bool mine = live && half == rnd;
-#pragma unroll
-                    for (int i = 0; i < kPairK; ++i) narrow_slot_add(mine && q + 16 * i < ne, c[i], v[i], diff, gs);
-#pragma unroll 1
-                    for (int k = q + 16 * kPairK; k < ne_max; k += 16) {
-                        if (mine && k < ne) {
-                            const unsigned idx = (unsigned)(kb - Ea + k) & kMask;
-                            const uint32_t ga = gs + 8u * (unsigned)lds_s32(cs + 4u * idx);
-                            sts_f64(ga, fma(diff, lds_f64(vs + 8u * idx), lds_f64(ga)));
-                        }
-                    }
-                    __syncwarp();
-                }
-            }
-            if (kPerRow && q == 0 && valid) {
-                if (kStats) {
-                    const double pr = round_half_up(acc + 0.0);
-                    stat_add(my_stat, y, pr);
-                    if (a.out_pred) a.out_pred[row] = pr;
-                    if (a.out_real) a.out_real[row] = y;
-                } else {
-                    a.out_pred[row] = acc + 0.0;
-                }
-            }
-        }
-#pragma unroll 1
-        while (released < (unsigned)ntiles) release_tile();
-        // a warp's (lossSum, count): row A's chain plus row B's chain
-        my_loss += shfl_xor_f64(my_loss, 16);
-        my_cnt += shfl_xor_f64(my_cnt, 16);
-    }
-    __syncthreads();
-
-    if (kTrain) {
-        double* out = a.partials + (long long)blockIdx.x * (d + 2);
-        for (int j = t; j < d; j += blockDim.x) {
-            double s = gacc[j];
-            for (int qq = 1; qq < W; ++qq) s += gacc[(size_t)qq * d + j];
-            out[j] = s;
-        }
-        if (lane == 0 && warp < W) { sred[2 * warp] = my_loss; sred[2 * warp + 1] = my_cnt; }
-        __syncthreads();
-        if (t == 0) {
-            double ls = 0.0, cn = 0.0;
-            for (int qq = 0; qq < W; ++qq) { ls += sred[2 * qq]; cn += sred[2 * qq + 1]; }
-            out[d] = ls;
-            out[d + 1] = cn;
-        }
-    }
-    if (kStats) {
-        double* sst = sred + 2 * kNarrowMaxWarps;
-        if (q != 0) stat_zero(my_stat);
-        narrow_warp_stat(my_stat);
-        if (lane == 0 && warp < W) stat_store(sst + warp * kStatStride, my_stat);
-        __syncthreads();
-        if (t == 0) {
-            Stat7 tot;
-            stat_zero(tot);
-            for (int qq = 0; qq < W; ++qq) {
-                Stat7 s2;
-                stat_load(s2, sst + qq * kStatStride);
-                stat_merge(tot, s2);
             }
             stat_store(a.stat_partials + (long long)blockIdx.x * kStatStride, tot);
         }

@@ -41,12 +41,6 @@ static int exclusive_sum(IngestLane& lane, const long long* in, long long* out, 
 
 static unsigned blocks_for(long long n, int threads) { return (unsigned)std::max<long long>(1, (n + threads - 1) / threads); }
 
-// A/B switches of the single-pass kernel (read once): TWTML_NARROW_PAIRS=1 row pairs (d <= 1024), TWTML_NARROW_STAGES=8 the
-// deeper entry ring.  Both change the launch shape fixed at ingest (warps per CTA), hence they are process-wide.
-static bool narrow_pairs_on() { static const bool on = getenv("TWTML_NARROW_PAIRS") != nullptr; return on; }
-static bool narrow_rows2_on() { static const bool on = getenv("TWTML_NARROW_ROWS2") != nullptr; return on; }
-static int narrow_stages() { static const int st = (getenv("TWTML_NARROW_STAGES") && atoi(getenv("TWTML_NARROW_STAGES")) == 8) ? 8 : kNarrowStages; return st; }
-
 // Narrow models: no transpose at all, only the first row of every CTA of the single-pass kernel.
 // Returns 1 when the batch does not qualify (the caller then builds the global transpose).
 static int csr_finalize_narrow(twtml_ctx* ctx, IngestLane& lane, twtml_batch* b)
@@ -54,11 +48,10 @@ static int csr_finalize_narrow(twtml_ctx* ctx, IngestLane& lane, twtml_batch* b)
     const long long n = b->n;
     const int d = (int)b->d;
     if (d > kNarrowMaxD || getenv("TWTML_NO_NARROW")) return 1; // a function of the model width only: every rank decides alike
-    int warps = narrow_warps(d, narrow_stages());
-    if (narrow_rows2_on()) warps = std::min(warps, kNarrow2MaxWarps);
+    const int warps = narrow_warps(d);
     if (warps < 4) return 1;
     // one partial vector per CTA of a grid fixed here: the plan's "blocks" are those CTAs
-    const long long grid = std::max<long long>(1, std::min<long long>((n + warps - 1) / warps, (long long)ctx->sm_count * narrow_ctas_per_sm(d)));
+    const long long grid = std::max<long long>(1, std::min<long long>((n + warps - 1) / warps, (long long)ctx->sm_count));
     TW_TRY(dev_alloc(ctx, lane, &b->bounds, (size_t)grid + 1));
     k_narrow_bounds<<<blocks_for(grid + 1, 256), 256, 0, lane.stream>>>(b->rowptr, n, grid, b->bounds);
     TW_CUDA(cudaGetLastError());
@@ -189,33 +182,22 @@ int csr_partial_width(const twtml_batch* b) { return (int)b->d + 2; }
 
 static int launch_narrow(twtml_ctx* ctx, const NarrowArgs& a, int mode, unsigned grid)
 {
-    const int stages = narrow_stages();
-    const size_t smem = narrow_smem_bytes(a.d, a.warps, stages);
-    const bool pairs = a.d <= kNarrowPairMaxD && narrow_pairs_on();
-    const bool rows2 = !pairs && narrow_rows2_on();
-    const unsigned form = 1u << ((pairs ? 4 : 0) + (stages == 8 ? 8 : 0) + (rows2 ? 16 : 0) + mode);
-#define TW_NARROW(KERNEL_, MODE_, ST_)                                                                           \
+    const size_t smem = narrow_smem_bytes(a.d, a.warps);
+#define TW_NARROW(MODE_)                                                                                         \
     do {                                                                                                         \
-        auto kern = KERNEL_<MODE_, ST_>;                                                                         \
-        if (!(ctx->narrow_attr_done & form)) { /* once per context (= per device) and kernel form */             \
+        auto kern = k_csr_narrow<MODE_>;                                                                         \
+        if (!(ctx->narrow_attr_done & (1u << MODE_))) { /* once per context (= per device) and kernel form */    \
             TW_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));        \
-            ctx->narrow_attr_done |= form;                                                                       \
+            ctx->narrow_attr_done |= 1u << MODE_;                                                                \
         }                                                                                                        \
         kern<<<grid, (a.warps + 1) * 32, smem, ctx->stream>>>(a);                                                \
     } while (0)
-#define TW_NARROW_MODE(KERNEL_, ST_)                                          \
-    switch (mode) {                                                           \
-    case MODE_TRAIN: TW_NARROW(KERNEL_, MODE_TRAIN, ST_); break;              \
-    case MODE_TRAIN_STATS: TW_NARROW(KERNEL_, MODE_TRAIN_STATS, ST_); break;  \
-    case MODE_PREDICT: TW_NARROW(KERNEL_, MODE_PREDICT, ST_); break;          \
-    default: TW_NARROW(KERNEL_, MODE_PREDICT_STATS, ST_); break;              \
+    switch (mode) {
+    case MODE_TRAIN: TW_NARROW(MODE_TRAIN); break;
+    case MODE_TRAIN_STATS: TW_NARROW(MODE_TRAIN_STATS); break;
+    case MODE_PREDICT: TW_NARROW(MODE_PREDICT); break;
+    default: TW_NARROW(MODE_PREDICT_STATS); break;
     }
-    if (stages == 8) {
-        if (pairs) { TW_NARROW_MODE(k_csr_narrow_pairs, 8) } else if (rows2) { TW_NARROW_MODE(k_csr_narrow2, 8) } else { TW_NARROW_MODE(k_csr_narrow, 8) }
-    } else {
-        if (pairs) { TW_NARROW_MODE(k_csr_narrow_pairs, kNarrowStages) } else if (rows2) { TW_NARROW_MODE(k_csr_narrow2, kNarrowStages) } else { TW_NARROW_MODE(k_csr_narrow, kNarrowStages) }
-    }
-#undef TW_NARROW_MODE
 #undef TW_NARROW
     TW_CUDA(cudaGetLastError());
     return 0;
