@@ -78,6 +78,9 @@ def test_two_gpus_match_one_gpu_bit_for_bit(tmp_path):
         assert res.returncode == 0 and "MGPU OK" in res.stdout, res.stdout[-2000:] + res.stderr[-2000:]
         outs[g] = np.load(out)
     for k in outs[1].files:
+        if k.startswith("csr"):      # CSR batches use one shard per rank: the sums differ in their last bits
+            assert np.allclose(outs[1][k], outs[2][k], rtol=1e-9, atol=1e-300), k
+            continue
         if not k[0].isdigit():       # "rep..." (iterations run by repeated calls) and "async" (n % 8 == 0): the same bits
             assert np.array_equal(outs[1][k], outs[2][k]), k
             continue
