@@ -273,6 +273,36 @@ int32_t twtml_train_on_batch(twtml_model* m, const twtml_batch* b, double* loss_
 int32_t twtml_step(twtml_model* m, const twtml_batch* b, double* out_real, double* out_pred_rounded,
                    twtml_stats* out, double* loss_history, int32_t cap, int32_t* iters_run);
 
+/* ---- the reference's second app: StreamingKMeans on (retweets, followers), KMeans.scala:69-113 ------------- */
+
+typedef struct twtml_kmeans twtml_kmeans; /* StreamingKMeans [U] state: k centres of dimension dim + their weights */
+
+/* new StreamingKMeans().setK(k) (KMeans.scala:69-70); 1 <= k, dim <= 16; single-GPU contexts. */
+int32_t twtml_kmeans_create(twtml_ctx* ctx, int32_t k, int32_t dim, twtml_kmeans** out);
+int32_t twtml_kmeans_free(twtml_kmeans* m);
+int32_t twtml_kmeans_set_decay_factor(twtml_kmeans* m, double a);                          /* .setDecayFactor (:71) */
+/* the timeUnit argument of StreamingKMeansModel.update (:98): 0 = "batches", 1 = "points" (discount = decay^points). */
+int32_t twtml_kmeans_set_time_unit(twtml_kmeans* m, int32_t time_unit);
+/* .setHalfLife(halfLife, timeUnit) (:72): decayFactor = exp(ln(0.5) / halfLife); time_unit 0 = "batches", 1 = "points". */
+int32_t twtml_kmeans_set_half_life(twtml_kmeans* m, double half_life, int32_t time_unit);
+/* .setInitialCenters(centers, weights): centers k x dim row-major. */
+int32_t twtml_kmeans_set_centers(twtml_kmeans* m, const double* centers, const double* weights);
+/* .setRandomCenters(dim, weight, seed) (:73): standard-normal centres, all weights = weight.  MLlib draws them from
+ * XORShiftRandom(seed); this library uses its own counter-based generator, so the centres differ from a JVM run's. */
+int32_t twtml_kmeans_set_random_centers(twtml_kmeans* m, double weight, uint64_t seed);
+/* latestModel.clusterCenters / clusterWeights (:101); either output may be null. */
+int32_t twtml_kmeans_get_centers(const twtml_kmeans* m, double* centers, double* weights);
+/* One batch interval of KMeans.scala:93-105 on n points (X row-major, stride ld >= dim):
+ *   standardize != 0: scaledData = new StandardScaler(false, true).fit(rdd).transform(rdd)   (:96; std_out[dim] receives
+ *       the fitted column standard deviations, unbiased, 0 for a single point; a column with std 0 scales to 0.0)
+ *   model.latestModel.update(scaledData, decayFactor, timeUnit)                              (:98)
+ *   assign_out[n] = model.latestModel.predict(scaledData) with the UPDATED centres           (:105)
+ * scaled_out[n x dim], std_out, assign_out are nullable.  n == 0 leaves the model untouched (`if (rdd.count > 0)`, :94). */
+int32_t twtml_kmeans_update(twtml_kmeans* m, const double* X, int64_t n, int64_t ld, int32_t standardize,
+                            double* std_out, double* scaled_out, int32_t* assign_out);
+/* latestModel.predict(points): index of the closest centre per point (ties: the lower index). */
+int32_t twtml_kmeans_predict(twtml_kmeans* m, const double* X, int64_t n, int64_t ld, int32_t* assign_out);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

@@ -20,8 +20,8 @@ _u8p = np.ctypeslib.ndpointer(np.uint8, flags="C_CONTIGUOUS")
 
 
 def build(force=False):
-    src = os.path.join(_HERE, "twtml_oracle.c")
-    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+    srcs = [os.path.join(_HERE, f) for f in ("twtml_oracle.c", "twtml_oracle_kmeans.c", "Makefile")]
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < max(os.path.getmtime(p) for p in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-s"], env=dict(os.environ))
     return _SO
 
@@ -185,3 +185,39 @@ def predict_stats(y, d, w, X=None, csr=None, partitions=1):
     st = dict(zip(keys, out.tolist()))
     st["batch"] = int(st["batch"])
     return st, praw[:n], prnd[:n]
+
+
+# ---- the reference's second app (KMeans.scala:93-105): StandardScaler + StreamingKMeansModel.update / predict -----------
+def column_std(X):
+    """StandardScaler(false, true).fit(rdd).std [U]: unbiased column standard deviations."""
+    X = np.ascontiguousarray(X, np.float64)
+    out = np.zeros(X.shape[1])
+    lib().twtml_oracle_column_std(_p(X), C.c_int64(X.shape[0]), C.c_int64(X.shape[1]), C.c_int32(X.shape[1]), _p(out))
+    return out
+
+
+def scale(X, std):
+    X = np.ascontiguousarray(X, np.float64)
+    std = np.ascontiguousarray(std, np.float64)
+    out = np.zeros_like(X)
+    lib().twtml_oracle_scale(_p(X), C.c_int64(X.shape[0]), C.c_int64(X.shape[1]), C.c_int32(X.shape[1]), _p(std), _p(out))
+    return out
+
+
+def kmeans_predict(centers, X):
+    centers = np.ascontiguousarray(centers, np.float64)
+    X = np.ascontiguousarray(X, np.float64)
+    out = np.zeros(max(X.shape[0], 1), np.int32)
+    lib().twtml_oracle_kmeans_predict(_p(centers), C.c_int32(centers.shape[0]), C.c_int32(centers.shape[1]), _p(X),
+                                      C.c_int64(X.shape[0]), C.c_int64(X.shape[1]), _p(out))
+    return out[:X.shape[0]]
+
+
+def kmeans_update(centers, weights, X, decay, time_unit=0):
+    """StreamingKMeansModel.update [U] -> (new centers, new weights); time_unit 0 batches, 1 points."""
+    c = np.array(centers, np.float64).copy()
+    w = np.array(weights, np.float64).copy()
+    X = np.ascontiguousarray(X, np.float64)
+    lib().twtml_oracle_kmeans_update(_p(c), _p(w), C.c_int32(c.shape[0]), C.c_int32(c.shape[1]), _p(X), C.c_int64(X.shape[0]),
+                                     C.c_int64(X.shape[1]), C.c_double(decay), C.c_int32(time_unit))
+    return c, w

@@ -192,3 +192,44 @@ def predict_stats(y, d, w, X=None, csr=None):
               pred_stdev=round_half_up(ps), mse_raw=mse, real_stdev_raw=rs, pred_stdev_raw=ps,
               real_mean=float(y.mean()), pred_mean=float(prnd.mean()))
     return st, raw, prnd
+
+
+# ---- KMeans.scala:93-105, written independently of the C file (vectorised; np.var for the scaler) ------------------------
+def column_std(X):
+    X = np.asarray(X, np.float64)
+    return np.sqrt(np.var(X, axis=0, ddof=1)) if X.shape[0] > 1 else np.zeros(X.shape[1])
+
+
+def scale(X, std):
+    inv = np.array([1.0 / s if s != 0.0 else 0.0 for s in std])
+    return np.asarray(X, np.float64) * inv
+
+
+def kmeans_predict(centers, X):
+    """Closest centre by squared Euclidean distance, ties to the lower index (exact differences: agrees with MLlib's
+    pruned / expanded form away from near-ties)."""
+    centers, X = np.asarray(centers, np.float64), np.asarray(X, np.float64)
+    d2 = ((X[:, None, :] - centers[None, :, :]) ** 2).sum(axis=2)
+    return np.argmin(d2, axis=1).astype(np.int32)
+
+
+def kmeans_update(centers, weights, X, decay, time_unit=0):
+    c, w = np.array(centers, np.float64), np.array(weights, np.float64)
+    X = np.asarray(X, np.float64)
+    lab = kmeans_predict(c, X)
+    w = w * (decay ** len(X) if time_unit == 1 else decay)
+    for k in range(len(c)):
+        pts = X[lab == k]
+        if len(pts) == 0:
+            continue
+        new_w = w[k] + len(pts)
+        lam = len(pts) / max(new_w, 1e-16)
+        c[k] = (1.0 - lam) * c[k] + lam * pts.mean(axis=0)
+        w[k] = new_w
+    big, small = int(np.argmax(w)), int(np.argmin(w))
+    if w[small] < 1e-8 * w[big]:
+        w[big] = w[small] = (w[big] + w[small]) / 2.0
+        p = 1e-14 * np.maximum(np.abs(c[big]), 1.0)
+        c[small] = c[big] - p
+        c[big] = c[big] + p
+    return c, w

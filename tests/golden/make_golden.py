@@ -185,4 +185,28 @@ stats = dict(w=[2, -1], X=[[1, 0], [0.75, 0], [0, 2.5], [0.1, 0]], y=[3, 2, -1, 
              batch=4, mse_raw=1.5, mse=2.0, real_stdev_raw=math.sqrt(2.1875), real_stdev=1.0,
              pred_stdev_raw=math.sqrt(4.1875), pred_stdev=2.0)
 dump("stats_kat.json", stats)
+# ------------------------------------------------------------------------------------------
+# 5. One interval of the k-means app (KMeans.scala:93-105), by hand, exact rationals.
+#    Points (already scaled; no StandardScaler) (0,0) (0,2) (10,0) (10,2) (11,1); centres c0 = (1,1), c1 = (9,1),
+#    weights (2, 0); decayFactor 1/2, "batches".
+#    Closest: p0, p1 -> c0 (dist 2 vs 82); p2, p3, p4 -> c1 (dist 2, 2, 4 vs 82, 82, 100).
+#    Discount: weights -> (1, 0).  c0: count 2, updated weight 3, lambda 2/3, mean (0,1): c0 = (1/3)(1,1) + (2/3)(0,1) = (1/3, 1)
+#    c1: count 3, updated weight 3, lambda 1, mean (31/3, 1): c1 = (31/3, 1).  No dying cluster (3 vs 3).
+#    Predict with the updated centres: p0, p1 -> 0; p2, p3, p4 -> 1.
+#    StandardScaler(false, true) on the raw columns x = (0,0,10,10,11), y = (0,2,0,2,1): unbiased variances
+#    x: mean 6.2, sum sq dev = 38.44*2 + 14.44*2 + 23.04 = 128.8 -> var 32.2 ; y: mean 1, sum sq dev 4 -> var 1.
+# ------------------------------------------------------------------------------------------
+km_pts = [[0, 0], [0, 2], [10, 0], [10, 2], [11, 1]]
+lam0 = Fr(2, 3)
+c0 = [float((1 - lam0) * 1 + lam0 * 0), float((1 - lam0) * 1 + lam0 * 1)]
+kmeans = dict(points=km_pts, centers=[[1, 1], [9, 1]], weights=[2, 0], decay=0.5, time_unit="batches",
+              closest_before=[0, 0, 1, 1, 1], centers_after=[c0, [float(Fr(31, 3)), 1.0]], weights_after=[3.0, 3.0],
+              closest_after=[0, 0, 1, 1, 1], column_std=[math.sqrt(32.2), 1.0],
+              # the same interval with "points": discount = (1/2)^5 -> weights (1/16, 0); c0: updated 33/16, lambda 32/33
+              centers_after_points=[[float(1 - Fr(32, 33)), 1.0], [float(Fr(31, 3)), 1.0]], weights_after_points=[2.0625, 3.0],
+              # a dying cluster: centres (1,1), (100,100), weights (4, 0): nobody joins c1 -> weights (2 + 5, 0) ->
+              # 0 < 1e-8 * 7: split c0 (updated first: lambda 5/7, mean (6.2, 1) -> c0 = (2/7)(1,1) + (5/7)(6.2, 1) = (33/7, 1))
+              dying=dict(centers=[[1, 1], [100, 100]], weights=[4, 0], weights_after=[3.5, 3.5],
+                         center_mid=[float(Fr(2, 7) + Fr(5, 7) * Fr(31, 5)), 1.0]))
+dump("kmeans_kat.json", kmeans)
 print("golden vectors written to", HERE)

@@ -81,6 +81,7 @@ def test_cpp_driver_loop_on_all_gpus_through_one_handle(tmp_path, oracle):
     one = subprocess.run([exe] + files, capture_output=True, text=True)
     many = subprocess.run([exe, "--devices", ",".join(str(i) for i in range(g))] + files, capture_output=True, text=True)
     assert one.returncode == 0 and many.returncode == 0, one.stdout + one.stderr + many.stdout + many.stderr
-    a, b = json.loads(one.stdout), json.loads(many.stdout)
+    last_json = lambda out: json.loads([l for l in out.splitlines() if l.startswith("{")][-1])   # libnccl prints its version first
+    a, b = last_json(one.stdout), last_json(many.stdout)
     assert a["batches"] == b["batches"]
     assert a["weights"] == b["weights"]                    # printed with %.17g: equal text means equal bits

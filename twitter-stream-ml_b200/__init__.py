@@ -6,7 +6,8 @@ importable by that name; `import twtml_b200` (the alias package at the repo root
 from . import _lib
 from ._lib import TwtmlError, build
 from .api import (Batch, Context, DenseVector, DStream, LabeledPoint, LinearRegressionModel, MllibHelper,
-                  SparseVector, StreamingLinearRegressionWithSGD, TweetBatch, Vectors, lightning_series, stats_payload)
+                  SparseVector, StandardScaler, StreamingKMeans, StreamingKMeansModel, StreamingLinearRegressionWithSGD, TweetBatch,
+                  Vectors, lightning_series, stats_payload)
 
 __all__ = ["Batch", "Context", "DenseVector", "DStream", "LabeledPoint", "LinearRegressionModel", "MllibHelper",
-           "SparseVector", "StreamingLinearRegressionWithSGD", "TweetBatch", "TwtmlError", "Vectors", "build", "lightning_series", "stats_payload", "_lib"]
+           "SparseVector", "StandardScaler", "StreamingKMeans", "StreamingKMeansModel", "StreamingLinearRegressionWithSGD", "TweetBatch", "TwtmlError", "Vectors", "build", "lightning_series", "stats_payload", "_lib"]

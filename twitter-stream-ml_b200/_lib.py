@@ -13,7 +13,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO_PATH = os.path.join(HERE, "libtwtml.so")
 HEADER = os.path.join(os.path.dirname(HERE), "include", "twtml.h")
-SOURCES = ["twtml.cu", "twtml_sparse.cu", "twtml_noalloc.cu", "twtml_group.cu"]
+SOURCES = ["twtml.cu", "twtml_sparse.cu", "twtml_noalloc.cu", "twtml_group.cu", "twtml_kmeans.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC,-fvisibility=hidden", "-shared"]
 
@@ -114,6 +114,16 @@ SIGNATURES = {
     "twtml_predict_stats_static": [_vp, _vp, C.POINTER(Stats)],
     "twtml_train_on_batch": [_vp, _vp, _vp, _i32, C.POINTER(_i32)],
     "twtml_step": [_vp, _vp, _vp, _vp, C.POINTER(Stats), _vp, _i32, C.POINTER(_i32)],
+    "twtml_kmeans_create": [_vp, _i32, _i32, C.POINTER(_vp)],
+    "twtml_kmeans_free": [_vp],
+    "twtml_kmeans_set_decay_factor": [_vp, _f64],
+    "twtml_kmeans_set_time_unit": [_vp, _i32],
+    "twtml_kmeans_set_half_life": [_vp, _f64, _i32],
+    "twtml_kmeans_set_centers": [_vp, _vp, _vp],
+    "twtml_kmeans_set_random_centers": [_vp, _f64, _u64],
+    "twtml_kmeans_get_centers": [_vp, _vp, _vp],
+    "twtml_kmeans_update": [_vp, _vp, _i64, _i64, _i32, _vp, _vp, _vp],
+    "twtml_kmeans_predict": [_vp, _vp, _i64, _i64, _vp],
 }
 
 

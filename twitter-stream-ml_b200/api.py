@@ -512,6 +512,165 @@ class StreamingLinearRegressionWithSGD:
         return stream.map(f)
 
 
+# ------------------------------------------------------------------------------------------------
+# the reference's second app (KMeans.scala): StandardScaler + StreamingKMeans, mirrored name for name
+# ------------------------------------------------------------------------------------------------
+class _Standardized:
+    """What StandardScalerModel.transform(rdd) returns in the reference (KMeans.scala:96): the batch's points together with
+    the request to scale them by the fitted column deviations.  The scaling itself runs on the GPU inside the model
+    update that consumes it; afterwards toArray() gives the scaled points (scaledData.map(_.apply(0)).toArray, :100-101)."""
+
+    def __init__(self, X):
+        self.X = np.ascontiguousarray(X, np.float64)
+        self.scaled = None
+        self.std = None
+
+    def count(self):
+        return self.X.shape[0]
+
+    def toArray(self):
+        if self.scaled is None:
+            raise ValueError("the scaled points exist once a StreamingKMeansModel.update has consumed this batch")
+        return self.scaled
+
+
+class StandardScaler:
+    """org.apache.spark.mllib.feature.StandardScaler [U] as KMeans.scala:96 uses it: withMean = false, withStd = true."""
+
+    def __init__(self, withMean=False, withStd=True):
+        if withMean or not withStd:
+            raise ValueError("only StandardScaler(false, true), the reference's configuration, is offered")
+
+    def fit(self, rdd):
+        return self                                      # the fit is part of the GPU call that consumes the batch
+
+    def transform(self, rdd):
+        return _Standardized(rdd)
+
+
+class StreamingKMeansModel:
+    """org.apache.spark.mllib.clustering.StreamingKMeansModel [U]: clusterCenters, clusterWeights, update, predict."""
+
+    def __init__(self, owner):
+        self._owner = owner
+
+    def _get(self):
+        o = self._owner
+        c, w = np.zeros((o._k, o._dim)), np.zeros(o._k)
+        try:
+            check(_lib.lib().twtml_kmeans_get_centers(o._m, ptr(c), ptr(w)))
+        except TwtmlError as e:
+            raise ValueError(e.message) if e.code == _lib.E_NOT_INITIALIZED else e
+        return c, w
+
+    @property
+    def clusterCenters(self):
+        return self._get()[0]
+
+    @property
+    def clusterWeights(self):
+        return self._get()[1]
+
+    def update(self, data, decayFactor, timeUnit):
+        """update(data, decayFactor, timeUnit) (KMeans.scala:98): data is an n x dim array, or what
+        StandardScaler(false, true).fit(rdd).transform(rdd) returned."""
+        o = self._owner
+        o._require("training")
+        L = _lib.lib()
+        check(L.twtml_kmeans_set_decay_factor(o._m, float(decayFactor)))
+        check(L.twtml_kmeans_set_time_unit(o._m, {"batches": 0, "points": 1}[timeUnit]))
+        std = isinstance(data, _Standardized)
+        X = data.X if std else np.ascontiguousarray(data, np.float64)
+        n = X.shape[0]
+        scaled = np.zeros((max(n, 1), o._dim)) if std else None
+        sd = np.zeros(o._dim) if std else None
+        check(L.twtml_kmeans_update(o._m, ptr(X), n, X.shape[1] if n else o._dim, int(std), ptr(sd), ptr(scaled), None))
+        if std:
+            data.scaled, data.std = scaled[:n], sd
+        return self
+
+    def predict(self, data):
+        o = self._owner
+        o._require("predictions")
+        X = data.toArray() if isinstance(data, _Standardized) else np.ascontiguousarray(data, np.float64)
+        out = np.zeros(max(X.shape[0], 1), np.int32)
+        check(_lib.lib().twtml_kmeans_predict(o._m, ptr(X), X.shape[0], X.shape[1] if X.shape[0] else o._dim, ptr(out)))
+        return out[:X.shape[0]]
+
+
+class StreamingKMeans:
+    """org.apache.spark.mllib.clustering.StreamingKMeans [U] as KMeans.scala:69-73 builds it."""
+    BATCHES, POINTS = "batches", "points"
+
+    def __init__(self, k=2, decayFactor=1.0, timeUnit="batches", ctx=None):
+        self.ctx = ctx if ctx is not None else Context(0)
+        self.ctx._children.add(self)
+        self._k, self._dim, self._m = int(k), None, None
+        self.decayFactor, self.timeUnit = float(decayFactor), timeUnit
+
+    def free(self):
+        if self._m is not None:
+            _lib.lib().twtml_kmeans_free(self._m)
+            self._m = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+    def setK(self, k):
+        self._k = int(k)
+        return self
+
+    def setDecayFactor(self, a):
+        self.decayFactor = float(a)
+        return self
+
+    def setHalfLife(self, halfLife, timeUnit):
+        if timeUnit not in ("batches", "points"):
+            raise ValueError("timeUnit must be 'batches' or 'points'")
+        self.decayFactor = float(np.exp(np.log(0.5) / halfLife))
+        self.timeUnit = timeUnit
+        return self
+
+    def _make(self, dim):
+        self.free()
+        self._dim = int(dim)
+        self._m = C.c_void_p()
+        check(_lib.lib().twtml_kmeans_create(self.ctx._h, self._k, self._dim, C.byref(self._m)))
+
+    def setInitialCenters(self, centers, weights):
+        centers = np.ascontiguousarray(centers, np.float64)
+        weights = np.ascontiguousarray(weights, np.float64)
+        if centers.shape[0] != self._k or weights.shape != (self._k,):
+            raise ValueError("need k centers and k weights")
+        self._make(centers.shape[1])
+        check(_lib.lib().twtml_kmeans_set_centers(self._m, ptr(centers), ptr(weights)))
+        return self
+
+    def setRandomCenters(self, dim, weight, seed=0):
+        self._make(dim)
+        check(_lib.lib().twtml_kmeans_set_random_centers(self._m, float(weight), int(seed)))
+        return self
+
+    def _require(self, what):
+        if self._m is None:     # StreamingKMeans.assertInitialized [U]
+            raise ValueError("Initial cluster centers must be set before starting %s" % what)
+
+    def latestModel(self):
+        self._require("predictions")
+        return StreamingKMeansModel(self)
+
+    def trainOn(self, stream):
+        self._require("training")
+        stream.foreachRDD(lambda rdd: self.latestModel().update(rdd, self.decayFactor, self.timeUnit))
+
+    def predictOn(self, stream):
+        self._require("predictions")
+        return stream.map(lambda rdd: self.latestModel().predict(rdd))
+
+
 def stats_payload(count, stats):
     """The JSON body SessionStats.update posts to twtml-web for one batch (SessionStats.scala:22-33 ->
     web/WebClient.scala:21-38, ApiTypes.scala:5-17; json4s ShortTypeHints put the class name under "jsonClass"):

@@ -492,6 +492,7 @@ static int check_tweet_args(twtml_ctx* ctx, twtml_batch** out, const TweetArgs& 
 // compute stream is needed before the first touch (nothing of it existed before)
 static int make_ready_event(twtml_batch* b)
 {
+    TW_CUDA(cudaSetDevice(b->ctx->device)); // an event belongs to the device that is current when it is made
     TW_CUDA(cudaEventCreateWithFlags(&b->ready, cudaEventDisableTiming));
     return 0;
 }
