@@ -179,8 +179,8 @@ int32_t twtml_batch_from_dense(twtml_ctx* ctx, int64_t n, int64_t d, const doubl
  * LinearRegression.scala:44-47,53,86).  X and labels must be page-locked host memory and stay
  * untouched until the batch has been used by a compute call or twtml_batch_ready(b, 1, ..) has
  * returned; with pageable memory the call simply behaves like twtml_batch_from_dense.  Works on
- * multi-rank contexts too: the ranks' row counts are then exchanged at the batch's first use (every
- * rank must use its batches in the same order, as with any collective). */
+ * multi-rank contexts too: the ranks' row counts are then exchanged by the first statistics or training
+ * call that uses the batch (the collective calls, which every rank makes in the same order anyway). */
 int32_t twtml_batch_from_dense_async(twtml_ctx* ctx, int64_t n, int64_t d, const double* X, int64_t ld_x,
                                      const double* labels, twtml_batch** out);
 

@@ -777,11 +777,10 @@ static void stop_worker(twtml_ctx* ctx)
 }
 
 // Host side of "is this batch usable": the worker's verdict for an asynchronously ingested batch (blocks until it is
-// in), the rows of a batch that is being appended to, and -- on a multi-rank context -- the row-count exchange an
-// asynchronous ingest left for later (it is a collective on the compute stream: every rank gets here with the same
-// batch in the same order, exactly as they all reach the training loop that follows).
+// in) and the rows of a batch that is being appended to.  Local: any rank may call it alone (export, ready, predict).
 int settle_batch(twtml_ctx* ctx, const twtml_batch* cb)
 {
+    (void)ctx;
     twtml_batch* b = const_cast<twtml_batch*>(cb);
     if (b->has_pending) {
         const int rc = b->pending.get();
@@ -789,6 +788,15 @@ int settle_batch(twtml_ctx* ctx, const twtml_batch* cb)
     }
     if (!b->csr && b->rows_appended < b->n)
         return fail(TWTML_E_INVALID_ARG, "batch used before all of its rows were appended (%lld of %lld)", (long long)b->rows_appended, (long long)b->n);
+    return 0;
+}
+
+// On a multi-rank context, the row-count exchange an asynchronous ingest left for later.  A collective on the compute
+// stream: only the collective compute calls (statistics, training) come here, where every rank arrives with the same
+// batch in the same order.
+static int resolve_global_rows(twtml_ctx* ctx, const twtml_batch* cb)
+{
+    twtml_batch* b = const_cast<twtml_batch*>(cb);
     if (b->global_deferred) {
         TW_TRY(ctx_global_rows(ctx, b->n, &b->n_global, &b->row0_global));
         b->global_deferred = false;
@@ -825,6 +833,7 @@ static int do_predict_stats(const twtml_model* m, const twtml_batch* b, double* 
 {
     twtml_ctx* ctx = m->ctx;
     TW_TRY(wait_ready(ctx, b));
+    TW_TRY(resolve_global_rows(ctx, b));
     if (b->n_global == 0) { stats_empty(out); return 0; }
     TW_TRY(reserve_scratch(ctx, m, b));
     double *dp = nullptr, *dr = nullptr;
@@ -848,6 +857,7 @@ static int do_train(twtml_model* m, const twtml_batch* b, bool with_stats, doubl
     if (iters_run) *iters_run = 0;
     ctx->prof = twtml_profile{};
     TW_TRY(wait_ready(ctx, b));
+    TW_TRY(resolve_global_rows(ctx, b));
     if (b->n_global == 0) { // rdd.isEmpty: both output ops skip the batch
         if (with_stats && out) stats_empty(out);
         return 0;
