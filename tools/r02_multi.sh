@@ -9,7 +9,7 @@ G=${2:-8}
 tr() { n=$1; shift; if [ "$n" = 1 ]; then python "$@"; else python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $((29600 + n)) "$@"; fi; }
 export -f tr
 { nvidia-smi --query-gpu=name,memory.total,pci.bus_id --format=csv; nproc; free -g | head -2; lscpu | grep -i -E "numa|socket|model name"; nvidia-smi topo -m; } > gpurun_out/${tag}_env.log 2>&1
-timeout 420 python -m pytest tests/test_group_gpu.py tests/test_cpp_facade.py tests/test_multi_rank.py -m gpu -q > gpurun_out/${tag}_pytest_multi.log 2>&1; grep -n "^E " gpurun_out/${tag}_pytest_multi.log | head -20; tail -4 gpurun_out/${tag}_pytest_multi.log
+timeout 420 python -m pytest tests/test_group_gpu.py tests/test_cpp_facade.py tests/test_multi_rank.py -m gpu -q --timeout 150 > gpurun_out/${tag}_pytest_multi.log 2>&1; grep -n "^E " gpurun_out/${tag}_pytest_multi.log | head -20; tail -4 gpurun_out/${tag}_pytest_multi.log
 timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $G --master-addr 127.0.0.1 --master-port 29700 tools/pcie_probe_multi.py 2>/dev/null | tail -1 > gpurun_out/${tag}_pcie_n$G.json; cat gpurun_out/${tag}_pcie_n$G.json
 for n in 1 2 4 8; do
   [ $n -le $G ] || continue

@@ -175,6 +175,7 @@ int settle_batch(twtml_ctx* ctx, const twtml_batch* b);
 int ctx_global_rows(twtml_ctx* ctx, int64_t n_local, int64_t* n_global, int64_t* row0);
 void make_plan(int64_t n_local, int spr, int R, Plan& p, int64_t min_blocks = 64);
 void batch_free_locked(twtml_batch* b);
+int prepare_compute(twtml_model* m, const twtml_batch* b, bool per_row_outputs);
 // batch memory from the context's pool, ordered on the compute stream
 int pool_alloc(twtml_ctx* ctx, void** p, size_t bytes, cudaStream_t stream = nullptr);
 void pool_free(twtml_ctx* ctx, void* p, cudaStream_t stream = nullptr);

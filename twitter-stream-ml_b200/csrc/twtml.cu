@@ -983,6 +983,25 @@ static int do_train(twtml_model* m, const twtml_batch* b, bool with_stats, doubl
     return 0;
 }
 
+// Everything a statistics / training call may allocate (scratch buffers, the per-row output staging, the wide exchange
+// buffer), done ahead of the call.  A device group runs this on all members first: an allocation on one member must not
+// fall into the time another member's kernels are already spinning on this member's flags.
+int prepare_compute(twtml_model* m, const twtml_batch* b, bool per_row_outputs)
+{
+    twtml_ctx* ctx = m->ctx;
+    Guard g(ctx);
+    TW_TRY(wait_ready(ctx, b));
+    TW_TRY(resolve_global_rows(ctx, b));
+    if (b->n_global == 0) return 0;
+    TW_TRY(reserve_scratch(ctx, m, b));
+    if (per_row_outputs) {
+        TW_TRY(ctx->tmp_a.reserve(sizeof(double) * (size_t)std::max<int64_t>(1, b->n)));
+        TW_TRY(ctx->tmp_b.reserve(sizeof(double) * (size_t)std::max<int64_t>(1, b->n)));
+    }
+    if (use_sliced_p2p(ctx, m, b)) TW_TRY(setup_wide_exchange(ctx, m->d));
+    return 0;
+}
+
 // caller holds the context lock (or is the only owner)
 void batch_free_locked(twtml_batch* b)
 {

@@ -444,6 +444,8 @@ int predict_stats(const twtml_model* m, const twtml_batch* b, double* out_real, 
 {
     const std::vector<int64_t> off = row_offsets(b);
     std::vector<twtml_stats> st(b->members.size());
+    // allocations first, on every member, before any member's kernels start waiting for the others
+    TW_TRY(m->ctx->threads->run([&](int r) { return prepare_compute(m->members[r], b->members[r], out_real || out_pred); }));
     TW_TRY(m->ctx->threads->run([&](int r) {
         return twtml_predict_stats(m->members[r], b->members[r], out_real ? out_real + off[r] : nullptr, out_pred ? out_pred + off[r] : nullptr, &st[r]);
     }));
@@ -459,6 +461,7 @@ int train(twtml_model* m, const twtml_batch* b, bool with_stats, double* out_rea
     std::vector<twtml_stats> st(W);
     std::vector<int32_t> it(W, 0);
     std::vector<std::vector<double>> hist(W, std::vector<double>((size_t)std::max(cap, 1)));
+    TW_TRY(m->ctx->threads->run([&](int r) { return prepare_compute(m->members[r], b->members[r], with_stats && (out_real || out_pred)); }));
     TW_TRY(m->ctx->threads->run([&](int r) {
         if (with_stats)
             return twtml_step(m->members[r], b->members[r], out_real ? out_real + off[r] : nullptr, out_pred ? out_pred + off[r] : nullptr, &st[r],
