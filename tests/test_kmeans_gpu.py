@@ -56,6 +56,10 @@ def test_kmeans_intervals_match_oracle(tw, ctx, oracle, n, k, dim):
         if t == 2:
             X[:, 0] = 7.0                                           # a constant column: deviation 0, scaled to 0.0
         scaled = tw.StandardScaler(False, True).fit(X).transform(X)
+        # every interval starts from the oracle's state, bit for bit: once a dying cluster has been split, two centres differ
+        # by 1e-14 (MLlib's own perturbation) and a last-bit difference between the two implementations' centres would hand
+        # the points between the twins to different sides
+        km.setInitialCenters(c, w)
         m = km.latestModel().update(scaled, km.decayFactor, km.timeUnit)
         sd = oracle.column_std(X)
         Xs = oracle.scale(X, sd)
