@@ -360,14 +360,10 @@ class Bench:
             streamed = False
             if tweets is not None:
                 names = ("text_utf16", "text_off", "retweet_count", "followers", "favourites", "friends", "created_ms", "is_retweet")
-                # the library ships only the tweets that pass MllibHelper.filtrate (the host evaluates it for the row count):
-                # their text, 33 bytes of columns and one text offset each
-                kept = (tweets.is_retweet != 0) & (tweets.retweet_count >= 100) & (tweets.retweet_count <= 1000)
-                lens = np.diff(tweets.text_off)
-                h2d = int(2 * lens[kept].sum() + 33 * kept.sum() + 8)
+                h2d = sum(getattr(tweets, k).nbytes for k in names)
                 ptweets = tw.TweetBatch.from_arrays(*(self.pin(getattr(tweets, k)) for k in names))
                 make = lambda: ctx.batch_from_tweets(ptweets, now_ms, 100, 1000, wl["buckets"], wait=self.args.e2e_sync)
-                how = "tweet columns -> host filter -> the %.0f %% of tweets that pass, through the pinned ring -> device featuriser" % (100.0 * kept.mean())
+                how = "page-locked tweet columns -> device featuriser"
             elif csr:
                 host = tuple(self.pin(a) for a in batch.export_csr())           # page-locked host copy of this rank's rows
                 h2d = sum(a.nbytes for a in host)

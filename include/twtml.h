@@ -153,8 +153,7 @@ int32_t twtml_num_features(const twtml_model* m, int64_t* d);
  *  now_ms: System.currentTimeMillis at MllibHelper.scala:61, injected.
  *  rt_begin/rt_end: numRetweetBegin/End (MllibHelper.scala:15-16), both inclusive.
  * The batch is CSR of width num_text_features + 4; rows failing the filter are dropped,
- * order kept.  n may be 0.  The host evaluates the filter too (it needs the row count) and copies only
- * the tweets that pass to the GPU -- .filter(filtrate) where the tweets are, .map(featurize) on the device. */
+ * order kept.  n may be 0. */
 #define TWTML_FLAG_LOWERCASE 1u
 int32_t twtml_batch_from_tweets(twtml_ctx* ctx, const uint16_t* text_utf16, const int64_t* text_off,
                                 const int32_t* retweet_cnt, const int32_t* followers,

@@ -169,9 +169,6 @@ struct twtml_batch {
 namespace twtml {
 // shared between twtml.cu and twtml_sparse.cu
 int upload_plain(twtml_ctx* ctx, IngestLane& lane, void* dst, const void* src, size_t bytes);
-int upload_gather(twtml_ctx* ctx, IngestLane& lane, void* dst, const void* src, size_t elem_bytes, const int64_t* idx, int64_t n);
-int upload_text_gather(twtml_ctx* ctx, IngestLane& lane, uint16_t* dst, const uint16_t* text, const int64_t* src_off, const int64_t* idx,
-                       const int64_t* dst_off, int64_t n);
 const char* last_error_text();
 int submit_ingest(twtml_ctx* ctx, twtml_batch* b, std::function<int()> job);
 int settle_batch(twtml_ctx* ctx, const twtml_batch* b);

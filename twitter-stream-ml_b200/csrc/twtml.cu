@@ -409,46 +409,6 @@ int upload_plain(twtml_ctx* ctx, IngestLane& lane, void* dst, const void* src, s
     });
 }
 
-// Host -> device copy of SELECTED elements of a column (src[idx[0]], src[idx[1]], ...): gathered on host threads into the
-// lane's pinned ring, chunk k+1 while chunk k is in flight.
-int upload_gather(twtml_ctx* ctx, IngestLane& lane, void* dst, const void* src, size_t elem_bytes, const int64_t* idx, int64_t n)
-{
-    (void)ctx;
-    const char* s = static_cast<const char*>(src);
-    return staged_upload(lane, dst, elem_bytes, n, [=](char* out, int64_t u0, int64_t nu) {
-        parallel_rows(nu, 1 << 16, [&](int64_t lo, int64_t hi) {
-            for (int64_t i = lo; i < hi; ++i) memcpy(out + (size_t)i * elem_bytes, s + (size_t)idx[u0 + i] * elem_bytes, elem_bytes);
-        });
-    });
-}
-
-// ... and of selected texts: tweet idx[i]'s UTF-16 units (text[src_off[idx[i]] ..)) land at dst + dst_off[i]
-int upload_text_gather(twtml_ctx* ctx, IngestLane& lane, uint16_t* dst, const uint16_t* text, const int64_t* src_off, const int64_t* idx,
-                       const int64_t* dst_off, int64_t n)
-{
-    (void)ctx;
-    if (n <= 0 || dst_off[n] == 0) return 0;
-    TW_TRY(ensure_pinned(lane, (size_t)32 << 20));
-    const int64_t cap = (int64_t)(lane.pin_bytes / sizeof(uint16_t)); // units per chunk; one tweet is far smaller
-    int k = 0;
-    for (int64_t i0 = 0; i0 < n; ++k) {
-        int64_t i1 = std::upper_bound(dst_off + i0, dst_off + n + 1, dst_off[i0] + cap) - dst_off - 1; // last tweet that still fits
-        if (i1 <= i0) i1 = i0 + 1;
-        const int bi = k & 1;
-        TW_CUDA(cudaEventSynchronize(lane.pin_ev[bi]));
-        uint16_t* out = static_cast<uint16_t*>(lane.pin[bi]);
-        const int64_t base = dst_off[i0];
-        parallel_rows(i1 - i0, 4096, [&](int64_t lo, int64_t hi) {
-            for (int64_t i = i0 + lo; i < i0 + hi; ++i)
-                memcpy(out + (dst_off[i] - base), text + src_off[idx[i]], sizeof(uint16_t) * (size_t)(dst_off[i + 1] - dst_off[i]));
-        });
-        TW_CUDA(cudaMemcpyAsync(dst + base, out, sizeof(uint16_t) * (size_t)(dst_off[i1] - base), cudaMemcpyHostToDevice, lane.stream));
-        TW_CUDA(cudaEventRecord(lane.pin_ev[bi], lane.stream));
-        i0 = i1;
-    }
-    return 0;
-}
-
 static bool page_locked(const void* p)
 {
     cudaPointerAttributes pa{};

@@ -9,7 +9,6 @@
 #include <atomic>
 #include <cmath>
 #include <cstring>
-#include <memory>
 #include <mutex>
 #include <thread>
 #include <vector>
@@ -367,28 +366,21 @@ struct TweetArgs {
     uint32_t flags;
 };
 
-// The tweets that pass MllibHelper.filtrate (:89-94), found on the host (all host threads): an asynchronously ingested batch
-// knows its row count (rdd.count, LinearRegression.scala:59) at once, and -- the filter keeps about one tweet in seven --
-// ONLY THOSE TWEETS ARE SHIPPED to the GPU: the stream's .filter(filtrate) runs where the tweets are, .map(featurize) on the
-// device (which evaluates the filter again on what it receives).  Also refuses texts the featuriser cannot hold.
-struct KeptTweets {
-    std::vector<int64_t> idx; // indices of the kept tweets, ascending
-    std::vector<int64_t> off; // their texts laid end to end: idx.size() + 1 offsets in UTF-16 units
-};
-
-static int tweets_precheck(const TweetArgs& t, KeptTweets& out)
+// rows that pass MllibHelper.filtrate (:89-94): the host can tell without the GPU, so an asynchronously ingested batch
+// knows its row count (rdd.count, LinearRegression.scala:59) at once; also refuses texts the featuriser cannot hold
+static int tweets_precheck(const TweetArgs& t, int64_t* n_kept)
 {
     const int nt = (int)std::max<int64_t>(1, std::min<int64_t>(std::min(16u, std::max(1u, std::thread::hardware_concurrency())), t.n / 65536));
-    std::vector<std::vector<int64_t>> kept((size_t)nt);
-    std::vector<int64_t> bad((size_t)nt, -1);
+    std::vector<int64_t> kept((size_t)nt, 0), bad((size_t)nt, -1);
     auto scan = [&](int k) { // a slice of the tweets on its own host thread
         const int64_t lo = t.n * k / nt, hi = t.n * (k + 1) / nt;
-        std::vector<int64_t>& mine = kept[(size_t)k];
+        int64_t c = 0;
         for (int64_t i = lo; i < hi; ++i) {
             const int64_t len = t.text_off[i + 1] - t.text_off[i];
             if ((len < 0 || len > kMaxTerms + 1) && bad[(size_t)k] < 0) bad[(size_t)k] = i;
-            if (t.is_retweet[i] != 0 && t.retweet_cnt[i] >= t.rt_begin && t.retweet_cnt[i] <= t.rt_end) mine.push_back(i);
+            c += t.is_retweet[i] != 0 && t.retweet_cnt[i] >= t.rt_begin && t.retweet_cnt[i] <= t.rt_end;
         }
+        kept[(size_t)k] = c;
     };
     if (nt == 1) scan(0);
     else {
@@ -396,28 +388,24 @@ static int tweets_precheck(const TweetArgs& t, KeptTweets& out)
         for (int k = 0; k < nt; ++k) th.emplace_back(scan, k);
         for (auto& x : th) x.join();
     }
-    size_t total = 0;
+    int64_t total = 0;
     for (int k = 0; k < nt; ++k) {
         if (bad[(size_t)k] >= 0) {
             const int64_t i = bad[(size_t)k], len = t.text_off[i + 1] - t.text_off[i];
             if (len < 0) return fail(TWTML_E_INVALID_ARG, "twtml_batch_from_tweets: text offsets decrease at tweet %lld", (long long)i);
             return fail(TWTML_E_INVALID_ARG, "a tweet has %lld UTF-16 units; the featuriser takes at most %d", (long long)len, kMaxTerms + 1);
         }
-        total += kept[(size_t)k].size();
+        total += kept[(size_t)k];
     }
-    out.idx.clear();
-    out.idx.reserve(total);
-    for (int k = 0; k < nt; ++k) out.idx.insert(out.idx.end(), kept[(size_t)k].begin(), kept[(size_t)k].end());
-    out.off.assign(total + 1, 0);
-    for (size_t i = 0; i < total; ++i) out.off[i + 1] = out.off[i] + (t.text_off[out.idx[i] + 1] - t.text_off[out.idx[i]]);
+    *n_kept = total;
     return 0;
 }
 
-static int tweets_ingest(twtml_ctx* ctx, IngestLane& lane, twtml_batch* b, const TweetArgs& t, const KeptTweets& kt, bool defer_global)
+static int tweets_ingest(twtml_ctx* ctx, IngestLane& lane, twtml_batch* b, const TweetArgs& t, bool defer_global)
 {
     std::lock_guard<std::mutex> lane_lock(lane.mu);
     cudaStream_t st = lane.stream;
-    const int64_t n = (int64_t)kt.idx.size(); // tweets that reach the device
+    const int64_t n = t.n;
     const int F = t.F;
     if (n == 0) {
         TW_TRY(csr_alloc(ctx, lane, b));
@@ -426,9 +414,8 @@ static int tweets_ingest(twtml_ctx* ctx, IngestLane& lane, twtml_batch* b, const
         if (b->ready) TW_CUDA(cudaEventRecord(b->ready, st));
         return 0;
     }
-    const int64_t units = kt.off[(size_t)n];
-    const int64_t* idx = kt.idx.data();
-    // device copies of the kept tweets' columns
+    const int64_t units = t.text_off[n];
+    // device copies of the tweet columns
     uint16_t* d_text = nullptr;
     long long *d_off = nullptr, *d_created = nullptr, *keep = nullptr, *rownnz = nullptr, *krow = nullptr, *eoff = nullptr;
     int *d_rc = nullptr, *d_fo = nullptr, *d_fa = nullptr, *d_fr = nullptr, *pair_idx = nullptr, *pair_cnt = nullptr;
@@ -451,14 +438,14 @@ static int tweets_ingest(twtml_ctx* ctx, IngestLane& lane, twtml_batch* b, const
     TW_OWN(dev_alloc(ctx, lane, &rownnz, (size_t)n + 1), rownnz);
     TW_OWN(dev_alloc(ctx, lane, &krow, (size_t)n + 1), krow);
     TW_OWN(dev_alloc(ctx, lane, &eoff, (size_t)n + 1), eoff);
-    TW_DO(upload_text_gather(ctx, lane, d_text, t.text_utf16, t.text_off, idx, kt.off.data(), n));
-    TW_DO(upload_plain(ctx, lane, d_off, kt.off.data(), sizeof(int64_t) * (size_t)(n + 1)));
-    TW_DO(upload_gather(ctx, lane, d_created, t.created_ms, sizeof(int64_t), idx, n));
-    TW_DO(upload_gather(ctx, lane, d_rc, t.retweet_cnt, sizeof(int32_t), idx, n));
-    TW_DO(upload_gather(ctx, lane, d_fo, t.followers, sizeof(int32_t), idx, n));
-    TW_DO(upload_gather(ctx, lane, d_fa, t.favourites, sizeof(int32_t), idx, n));
-    TW_DO(upload_gather(ctx, lane, d_fr, t.friends, sizeof(int32_t), idx, n));
-    TW_DO(upload_gather(ctx, lane, d_rt, t.is_retweet, 1, idx, n));
+    if (units) TW_DO(upload_plain(ctx, lane, d_text, t.text_utf16, sizeof(uint16_t) * (size_t)units));
+    TW_DO(upload_plain(ctx, lane, d_off, t.text_off, sizeof(int64_t) * (size_t)(n + 1)));
+    TW_DO(upload_plain(ctx, lane, d_created, t.created_ms, sizeof(int64_t) * (size_t)n));
+    TW_DO(upload_plain(ctx, lane, d_rc, t.retweet_cnt, sizeof(int32_t) * (size_t)n));
+    TW_DO(upload_plain(ctx, lane, d_fo, t.followers, sizeof(int32_t) * (size_t)n));
+    TW_DO(upload_plain(ctx, lane, d_fa, t.favourites, sizeof(int32_t) * (size_t)n));
+    TW_DO(upload_plain(ctx, lane, d_fr, t.friends, sizeof(int32_t) * (size_t)n));
+    TW_DO(upload_plain(ctx, lane, d_rt, t.is_retweet, (size_t)n));
 
     const uint16_t* lower = nullptr;
     if (t.flags & TWTML_FLAG_LOWERCASE) TW_DO(lower_table(ctx, &lower));
@@ -469,7 +456,7 @@ static int tweets_ingest(twtml_ctx* ctx, IngestLane& lane, twtml_batch* b, const
     k_feat_terms<<<gridA, kFeatWarps * 32, 0, st>>>(tc, n, t.rt_begin, t.rt_end, F, lower, pair_idx, pair_cnt, keep, rownnz);
     TW_DO(exclusive_sum(lane, keep, krow, n + 1));
     TW_DO(exclusive_sum(lane, rownnz, eoff, n + 1));
-    // the one size only the device knows: how many entries the rows have (the row count was settled on the host)
+    // the one size only the device knows: how many entries the kept rows have (the row count was settled on the host)
     long long tot[2] = {0, 0};
     cudaMemcpyAsync(&tot[0], krow + n, sizeof(long long), cudaMemcpyDeviceToHost, st);
     cudaMemcpyAsync(&tot[1], eoff + n, sizeof(long long), cudaMemcpyDeviceToHost, st);
@@ -598,11 +585,11 @@ int32_t twtml_batch_from_tweets(twtml_ctx* ctx, const uint16_t* text_utf16, cons
     if (!ctx->members.empty())
         return grp::from_tweets(ctx, grp::TweetCols{text_utf16, text_off, retweet_cnt, followers, favourites, friends, created_ms, is_retweet}, n, now_ms,
                                 rt_begin, rt_end, num_text_features, flags, false, out);
-    KeptTweets kt;
-    TW_TRY(tweets_precheck(t, kt));
+    int64_t kept = 0;
+    TW_TRY(tweets_precheck(t, &kept));
     Guard g(ctx);
-    twtml_batch* b = csr_shell(ctx, (int64_t)kt.idx.size(), (int64_t)num_text_features + 4, 0);
-    int rc = tweets_ingest(ctx, ctx->lane[0], b, t, kt, false);
+    twtml_batch* b = csr_shell(ctx, kept, (int64_t)num_text_features + 4, 0);
+    int rc = tweets_ingest(ctx, ctx->lane[0], b, t, false);
     if (!rc && cudaStreamSynchronize(ctx->stream) != cudaSuccess) rc = fail(TWTML_E_CUDA, "tweet ingest failed: %s", cudaGetErrorString(cudaGetLastError()));
     if (rc) { batch_free_locked(b); return rc; }
     *out = b;
@@ -619,11 +606,11 @@ int32_t twtml_batch_from_tweets_async(twtml_ctx* ctx, const uint16_t* text_utf16
     if (!ctx->members.empty())
         return grp::from_tweets(ctx, grp::TweetCols{text_utf16, text_off, retweet_cnt, followers, favourites, friends, created_ms, is_retweet}, n, now_ms,
                                 rt_begin, rt_end, num_text_features, flags, true, out);
-    auto kt = std::make_shared<KeptTweets>();
-    TW_TRY(tweets_precheck(t, *kt));
-    twtml_batch* b = csr_shell(ctx, (int64_t)kt->idx.size(), (int64_t)num_text_features + 4, 0);
+    int64_t kept = 0;
+    TW_TRY(tweets_precheck(t, &kept));
+    twtml_batch* b = csr_shell(ctx, kept, (int64_t)num_text_features + 4, 0);
     if (int rc = make_ready_event(b)) { Guard g(ctx); batch_free_locked(b); return rc; }
-    submit_ingest(ctx, b, [=]() { return tweets_ingest(ctx, ctx->lane[1], b, t, *kt, true); });
+    submit_ingest(ctx, b, [=]() { return tweets_ingest(ctx, ctx->lane[1], b, t, true); });
     *out = b;
     return 0;
 }
