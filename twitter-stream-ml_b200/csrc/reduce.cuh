@@ -47,31 +47,56 @@ static __global__ void __launch_bounds__(1024) k_shard_reduce(const double* __re
 }
 
 // ---- exchange of the shard vectors over peer memory (NVLink) ------------------------------------
-// Every rank owns one exchange buffer: data[2 parities][kMaxShards][kPvCap] doubles, then
-// flags[2][kMaxShards] (one per writer rank), then a CTA counter.  All ranks map all buffers (CUDA IPC
-// between processes, direct peer access between threads of one process).  In iteration number seq a
-// rank's k_shard_reduce_p2p stores its shard vectors straight into EVERY rank's buffer (parity seq & 1)
-// and, once its last CTA is done, stores seq into its flag slot on every rank; the update kernel of a
-// rank spins on its own flag slots until all writers have reached seq.
+// Every rank owns one exchange buffer: lines[2 parities][kMaxShards * kPvCap] of 16 bytes, then the number of the
+// last exchange this rank completed.  All ranks map all buffers (CUDA IPC between processes, direct peer access
+// between threads of one process).  A line carries one double together with the number of the exchange it belongs
+// to: {low word, seq} {high word, seq}, two 8-byte halves, each stored and loaded whole.  In exchange number seq a
+// rank's k_shard_reduce_p2p stores every element of its shard vectors as such a line straight into EVERY rank's
+// buffer (parity seq & 1); the update kernel of a rank reads a line until both halves show seq, and then holds the
+// value.  Data and "it has arrived" travel in the same store, so the exchange costs one trip over NVLink and needs
+// no fence, no counter and no separate flag (the first form of this exchange -- vectors, a system-scope fence, a
+// flag per writer, another fence on the reading side -- took two round trips and measured slower than NCCL's
+// all-gather on the 8 KB vectors of the 1004-column model: profiles/r02_SUMMARY.md).
 // The sequence number lives ON THE DEVICE (one word of the local buffer, advanced by the update kernel
 // after it has read the vectors): it counts the exchanges that really ran, not the launches the host
 // enqueued -- after an early convergence the remaining launches of a call are no-ops and leave it alone.
 // Every rank takes the same decisions from the same bits, so the words stay equal across ranks.  Two
-// parities then suffice: a rank starts exchange seq + 2 only after its update kernel saw every flag at
-// seq + 1, i.e. after every peer's update kernel of exchange seq has finished reading parity seq & 1.
+// parities then suffice: a rank starts exchange seq + 2 only after its update kernel has read every line of
+// exchange seq + 1, which a peer sends only after its own update kernel of exchange seq has finished reading
+// parity seq & 1.  The buffer starts zeroed and seq at 1, so a line never written never matches.
 constexpr int kPvCap = 4104;
-constexpr size_t kXbufDataDoubles = (size_t)2 * kMaxShards * kPvCap;
-constexpr size_t kXbufBytes = kXbufDataDoubles * 8 + 2 * kMaxShards * 8 + 64;
+constexpr size_t kXbufLines = (size_t)2 * kMaxShards * kPvCap;
+constexpr size_t kXbufBytes = kXbufLines * 16 + 64;
 
 struct PeerExchange {
     double* peer[kMaxShards]; // base of rank r's exchange buffer, as mapped here
     int world, rank;
 };
 
-__host__ __device__ __forceinline__ unsigned long long* xbuf_flags(double* base) { return reinterpret_cast<unsigned long long*>(base + kXbufDataDoubles); }
-// local words behind the flags: the CTA counter of k_shard_reduce_p2p and the number of the last exchange this rank completed
-__host__ __device__ __forceinline__ unsigned* xbuf_counter(double* base) { return reinterpret_cast<unsigned*>(xbuf_flags(base) + 2 * kMaxShards); }
-__host__ __device__ __forceinline__ unsigned long long* xbuf_seq(double* base) { return xbuf_flags(base) + 2 * kMaxShards + 1; }
+__host__ __device__ __forceinline__ ulonglong2* xbuf_lines(double* base, int parity)
+{
+    return reinterpret_cast<ulonglong2*>(base) + (size_t)parity * kMaxShards * kPvCap;
+}
+// local word behind the lines: the number of the last exchange this rank completed
+__host__ __device__ __forceinline__ unsigned long long* xbuf_seq(double* base) { return reinterpret_cast<unsigned long long*>(base) + 2 * kXbufLines; }
+
+__device__ __forceinline__ void ll_store(ulonglong2* line, double v, unsigned tag)
+{
+    const unsigned long long bits = (unsigned long long)__double_as_longlong(v), t = (unsigned long long)tag << 32;
+    const unsigned long long lo = (bits & 0xffffffffull) | t, hi = (bits >> 32) | t;
+    asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(line), "l"(lo), "l"(hi) : "memory");
+}
+__device__ __forceinline__ ulonglong2 ll_load(const ulonglong2* line)
+{
+    ulonglong2 v;
+    asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(line) : "memory");
+    return v;
+}
+__device__ __forceinline__ bool ll_ready(const ulonglong2& v, unsigned tag) { return (unsigned)(v.x >> 32) == tag && (unsigned)(v.y >> 32) == tag; }
+__device__ __forceinline__ double ll_value(const ulonglong2& v)
+{
+    return __longlong_as_double((long long)((v.x & 0xffffffffull) | (v.y << 32)));
+}
 
 static __global__ void __launch_bounds__(1024) k_shard_reduce_p2p(const double* __restrict__ partials, int pv, Plan plan, PeerExchange px,
                                                            const TrainState* state)
@@ -97,27 +122,15 @@ static __global__ void __launch_bounds__(1024) k_shard_reduce_p2p(const double* 
     }
     sm[threadIdx.y][threadIdx.x] = acc;
     __syncthreads();
-    double* mine = px.peer[px.rank];
-    const unsigned long long seq = *xbuf_seq(mine) + 1ull; // advanced only by the update kernel that follows on this stream
+    const unsigned long long seq = *xbuf_seq(px.peer[px.rank]) + 1ull; // advanced only by the update kernel that follows on this stream
     const int parity = (int)(seq & 1ull);
-    if (threadIdx.y == 0 && col < pv) {
+    // the 32 columns of this CTA go to the world's buffers, one warp row per destination rank
+    if ((int)threadIdx.y < px.world && col < pv) {
         double tot = 0.0;
 #pragma unroll
         for (int q = 0; q < 32; ++q) tot += sm[q][threadIdx.x];
-        const size_t slot = (size_t)parity * kMaxShards * kPvCap + ((size_t)px.rank * plan.spr + s) * pv + col; // packed nshards x pv like the NCCL path
-        for (int r = 0; r < px.world; ++r) px.peer[r][slot] = tot;
-        __threadfence_system();
-    }
-    __syncthreads();
-    if (threadIdx.x == 0 && threadIdx.y == 0) {
-        const unsigned total = gridDim.x * gridDim.y;
-        unsigned* counter = xbuf_counter(mine);
-        if (atomicAdd(counter, 1u) == total - 1u) { // last CTA of this rank: everything above is globally visible
-            *counter = 0u;
-            __threadfence_system();
-            for (int r = 0; r < px.world; ++r)
-                *reinterpret_cast<volatile unsigned long long*>(xbuf_flags(px.peer[r]) + parity * kMaxShards + px.rank) = seq;
-        }
+        const size_t slot = ((size_t)px.rank * plan.spr + s) * pv + col; // packed nshards x pv like the NCCL path
+        for (int r = threadIdx.y; r < px.world; r += 32) ll_store(xbuf_lines(px.peer[r], parity) + slot, tot, (unsigned)seq);
     }
 }
 
@@ -144,38 +157,50 @@ struct UpdateArgs {
     int nshards, pv, d, ldx;
     int max_iter, updater;
     double step, reg, tol;
-    // peer exchange (xbuf != null): the vectors of exchange seq = *xbuf_seq + 1 are read from this rank's exchange buffer
-    // once its wait_n writers have stored seq into their flag slots; `shards` is then ignored
+    // peer exchange (xbuf != null): the nshards x pv lines of exchange seq = *xbuf_seq + 1 are read from this rank's
+    // exchange buffer as they arrive and left in `shards` (then this rank's staging copy)
     double* xbuf;
-    int wait_n;
     int* host_done; // mapped host word set when the loop is over, so a single-GPU host can stop enqueuing no-op iterations
 };
 
 constexpr int kPeerTimeoutMark = 0x7E57; // TrainState::pad after a peer never showed up
 
-// Peer exchange: points a.shards at this exchange's vectors and waits for every writer.  Returns false when a peer did
-// not arrive within ~10 s (the kernel then stops the training loop).  The writers are other GPUs: the flags are read
-// with system-scope volatile loads, every thread fences at system scope before it touches the vectors, and the
-// vectors themselves are read past L1 (__ldcg in update_column / shard_totals).
+// Peer exchange: collects this exchange's lines into a.shards as their writers (this GPU among them) deliver them.
+// Returns false when a line did not arrive within ~10 s (the kernel then stops the training loop).  A thread asks for
+// four lines before it looks at the first, so the waits of one thread overlap.
 __device__ __forceinline__ bool wait_for_peers(UpdateArgs& a, unsigned long long& seq)
 {
     __shared__ int timed_out;
     seq = 0ull;
     if (!a.xbuf) return true;
     seq = *xbuf_seq(a.xbuf) + 1ull;
-    const int parity = (int)(seq & 1ull);
-    a.shards = a.xbuf + (size_t)parity * kMaxShards * kPvCap;
+    const unsigned tag = (unsigned)seq;
+    const ulonglong2* lines = xbuf_lines(a.xbuf, (int)(seq & 1ull));
+    double* stage = const_cast<double*>(a.shards);
+    const int total = a.nshards * a.pv;
     if (threadIdx.x == 0) timed_out = 0;
     __syncthreads();
-    if (threadIdx.x < a.wait_n) {
-        const volatile unsigned long long* f = xbuf_flags(a.xbuf) + parity * kMaxShards + threadIdx.x;
-        const long long t0 = clock64();
-        while (*f < seq)
-            if (clock64() - t0 > 20000000000ll) { timed_out = 1; break; }
-        __threadfence_system();
+    const long long t0 = clock64();
+    constexpr int U = 4;
+    for (int base = 0; base < total; base += U * (int)blockDim.x) {
+        ulonglong2 v[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int idx = base + u * (int)blockDim.x + (int)threadIdx.x;
+            if (idx < total) v[u] = ll_load(lines + idx);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int idx = base + u * (int)blockDim.x + (int)threadIdx.x;
+            if (idx >= total) continue;
+            while (!ll_ready(v[u], tag)) {
+                if (clock64() - t0 > 20000000000ll) { timed_out = 1; break; }
+                v[u] = ll_load(lines + idx);
+            }
+            stage[idx] = ll_value(v[u]);
+        }
     }
-    __syncthreads();
-    __threadfence_system();
+    __syncthreads(); // the staging copy is complete for every thread of this CTA
     if (timed_out) {
         if (threadIdx.x == 0) { a.state->done = 1; a.state->pad = kPeerTimeoutMark; }
         return false;
@@ -285,10 +310,14 @@ static __global__ void __launch_bounds__(1024) k_update(const UpdateArgs a_in)
 // then complete and visible) goes on to be k_update.  The update reads spr vectors of pv doubles, not the block partials,
 // so the extra work of that one CTA is small; one launch and one dependent-launch gap per SGD iteration are saved, which
 // is what a 13-row batch interval or a 70 us tweet iteration notices.  Same arithmetic in the same order as the pair.
+// P2P (several ranks): the vectors go out as lines of the peer exchange instead (k_shard_reduce_p2p), and the last CTA
+// collects every rank's lines before it updates (k_update with a.xbuf set).
+template <bool P2P>
 static __global__ void __launch_bounds__(1024) k_shard_reduce_update(const double* __restrict__ partials, int pv, Plan plan,
                                                               double* __restrict__ shard_out, unsigned* __restrict__ counter,
-                                                              const UpdateArgs a)
+                                                              const UpdateArgs a_in, const PeerExchange px)
 {
+    UpdateArgs a = a_in;
     __shared__ double sm[32][33];
     __shared__ double sm32[32];
     __shared__ int is_last;
@@ -313,7 +342,16 @@ static __global__ void __launch_bounds__(1024) k_shard_reduce_update(const doubl
     }
     sm[ty][tx] = acc;
     __syncthreads();
-    if (ty == 0 && col < pv) {
+    if (P2P) {
+        const unsigned long long seq = *xbuf_seq(px.peer[px.rank]) + 1ull; // read before this CTA's ticket: the update that advances it starts after the last ticket
+        if (ty < px.world && col < pv) {
+            double tot = 0.0;
+#pragma unroll
+            for (int q = 0; q < 32; ++q) tot += sm[q][tx];
+            const size_t slot = ((size_t)px.rank * plan.spr + s) * pv + col;
+            for (int r = ty; r < px.world; r += 32) ll_store(xbuf_lines(px.peer[r], (int)(seq & 1ull)) + slot, tot, (unsigned)seq);
+        }
+    } else if (ty == 0 && col < pv) {
         double tot = 0.0;
 #pragma unroll
         for (int q = 0; q < 32; ++q) tot += sm[q][tx];
@@ -328,7 +366,12 @@ static __global__ void __launch_bounds__(1024) k_shard_reduce_update(const doubl
     }
     __syncthreads();
     if (!is_last) return;
-    __threadfence();
+    unsigned long long seq = 0ull;
+    if (P2P) {
+        if (!wait_for_peers(a, seq)) return; // (lines announce themselves: no fence)
+    } else {
+        __threadfence();
+    }
     double cnt, loss;
     shard_totals(a, loss, cnt);
     double dn2 = 0.0, wn2 = 0.0, l1 = 0.0;
@@ -339,7 +382,10 @@ static __global__ void __launch_bounds__(1024) k_shard_reduce_update(const doubl
     dn2 = block_sum_1024(dn2, sm32);
     wn2 = block_sum_1024(wn2, sm32);
     l1 = block_sum_1024(l1, sm32);
-    if (threadIdx.x == 0) finish_iteration(a, loss, cnt, dn2, wn2, l1);
+    if (threadIdx.x == 0) {
+        finish_iteration(a, loss, cnt, dn2, wn2, l1);
+        if (P2P) *xbuf_seq(a.xbuf) = seq; // this exchange is complete on this rank
+    }
 }
 
 // Wide models (hashed text, d ~ 2^20): the columns are spread over many CTAs, each leaving its three

@@ -681,7 +681,9 @@ static int sliced_update(twtml_ctx* ctx, twtml_model* m, const twtml_batch* b, c
 
 static bool use_p2p(const twtml_ctx* ctx, const twtml_batch* b)
 {
-    return ctx->p2p_ok && !b->csr && partial_width(b) <= kPvCap && b->plan.spr * ctx->world <= kMaxShards;
+    static const bool csr_nccl = getenv("TWTML_NO_P2P_NARROW") != nullptr; // A/B switch: narrow CSR over NCCL as in round 1
+    if (b->csr && (!b->narrow || csr_nccl)) return false;
+    return ctx->p2p_ok && partial_width(b) <= kPvCap && b->plan.spr * ctx->world <= kMaxShards;
 }
 
 static int exchange_shards(twtml_ctx* ctx, const twtml_batch* b)
@@ -695,10 +697,11 @@ static int reduce_local(twtml_ctx* ctx, const twtml_batch* b, bool gated, bool w
     const int pv = partial_width(b), spr = b->plan.spr;
     const TrainState* gate = gated ? ctx->state.as<TrainState>() : nullptr;
     double* mine = ctx->shards.as<double>() + (size_t)ctx->rank * spr * pv;
-    if (b->csr) {
+    const bool p2p = gated && use_p2p(ctx, b); // dense, or the 1004-column CSR model whose CTAs leave the same kind of vectors
+    if (b->csr && !p2p) {
         if (wide_p2p) mine = wx_G(ctx->wxbuf); // the peers read the gradient where the column pass leaves it
         TW_TRY(csr_reduce(ctx, b, mine, gate));
-    } else if (gated && use_p2p(ctx, b)) {
+    } else if (p2p) {
         PeerExchange px{};
         for (int r = 0; r < ctx->world; ++r) px.peer[r] = ctx->peer[r];
         px.world = ctx->world;
@@ -902,7 +905,14 @@ static int do_train(twtml_model* m, const twtml_batch* b, bool with_stats, doubl
         wide_p2p = !ctx->wx_failed && ctx->wxbuf != nullptr;
     }
     static const bool no_fuse = getenv("TWTML_NO_FUSED_TAIL") != nullptr; // A/B switch
-    const bool fused_tail = ctx->world == 1 && !no_fuse && m->d <= 2 * kWideCols && (!b->csr || b->narrow);
+    const bool p2p = ctx->world > 1 && use_p2p(ctx, b);
+    const bool fused_tail = (ctx->world == 1 || p2p) && !no_fuse && m->d <= 2 * kWideCols && (!b->csr || b->narrow);
+    PeerExchange px{};
+    if (p2p) {
+        for (int r = 0; r < ctx->world; ++r) px.peer[r] = ctx->peer[r];
+        px.world = ctx->world;
+        px.rank = ctx->rank;
+    }
     const bool prof = ctx->profiling;
     size_t ne = 0;
     if (prof) TW_CUDA(cudaEventRecord(prof_event(ctx, ne++), ctx->stream));
@@ -917,10 +927,15 @@ static int do_train(twtml_model* m, const twtml_batch* b, bool with_stats, doubl
         const bool one_kernel = !b->csr || b->narrow;
         if (prof && one_kernel) TW_CUDA(cudaEventRecord(prof_event(ctx, ne++), ctx->stream));
         ctx->prof.iter_launches += 1;
-        if (fused_tail) { // one GPU, narrow model: shard reduce + update in one launch
+        if (fused_tail) { // narrow model: shard reduce (+ the exchange over peer memory) + update in one launch
             const int spr = b->plan.spr;
             dim3 grid((pv + 31) / 32, spr);
-            k_shard_reduce_update<<<grid, 1024, 0, ctx->stream>>>(ctx->partials.as<double>(), pv, b->plan, ctx->shards.as<double>(), fuse_counter, ua);
+            if (p2p) {
+                ua.xbuf = ctx->xbuf;
+                k_shard_reduce_update<true><<<grid, 1024, 0, ctx->stream>>>(ctx->partials.as<double>(), pv, b->plan, ctx->shards.as<double>(), fuse_counter, ua, px);
+            } else {
+                k_shard_reduce_update<false><<<grid, 1024, 0, ctx->stream>>>(ctx->partials.as<double>(), pv, b->plan, ctx->shards.as<double>(), fuse_counter, ua, px);
+            }
             TW_CUDA(cudaGetLastError());
             ctx->prof.other_launches += 1;
             if (i == 1 && with_stats) TW_TRY(reduce_stats(ctx, b));
@@ -936,7 +951,6 @@ static int do_train(twtml_model* m, const twtml_batch* b, bool with_stats, doubl
         TW_TRY(exchange_shards(ctx, b));
         if (use_p2p(ctx, b)) { // read this iteration's vectors from the local exchange buffer once every writer has signalled
             ua.xbuf = ctx->xbuf;
-            ua.wait_n = ctx->world;
         }
         if (m->d <= 2 * kWideCols) {
             k_update<<<1, 1024, 0, ctx->stream>>>(ua);
