@@ -360,10 +360,19 @@ class Bench:
             streamed = False
             if tweets is not None:
                 names = ("text_utf16", "text_off", "retweet_count", "followers", "favourites", "friends", "created_ms", "is_retweet")
-                h2d = sum(getattr(tweets, k).nbytes for k in names)
+                h2d = host_input = sum(getattr(tweets, k).nbytes for k in names)
                 ptweets = tw.TweetBatch.from_arrays(*(self.pin(getattr(tweets, k)) for k in names))
                 make = lambda: ctx.batch_from_tweets(ptweets, now_ms, 100, 1000, wl["buckets"], wait=self.args.e2e_sync)
                 how = "page-locked tweet columns -> device featuriser"
+                if 2 * n <= n_tweets and not os.environ.get("TWTML_NO_TEXT_IN_PLACE"):
+                    # twtml_sparse.cu tweets_ingest: the text column stays in host memory; the featuriser reads the text of
+                    # the tweets that pass the filter over the host link, inside the timed region
+                    kept = (tweets.is_retweet != 0) & (tweets.retweet_count >= 100) & (tweets.retweet_count <= 1000)
+                    assert int(kept.sum()) == n
+                    kept_text = 2 * int(np.diff(tweets.text_off)[kept].sum())
+                    h2d = host_input - tweets.text_utf16.nbytes + kept_text
+                    how = ("page-locked tweet columns -> device featuriser; the text column (%d B) is read in place, %d B of it "
+                           "(the kept tweets') cross the link" % (tweets.text_utf16.nbytes, kept_text))
             elif csr:
                 host = tuple(self.pin(a) for a in batch.export_csr())           # page-locked host copy of this rank's rows
                 h2d = sum(a.nbytes for a in host)
@@ -391,6 +400,7 @@ class Bench:
                            % (CHUNK_ROWS, (n + CHUNK_ROWS - 1) // CHUNK_ROWS))
             model.setInitialWeights(tw.Vectors.zeros(d))
             t_ingest = t_step = 0.0
+            step_ms = []
 
             def run(k):
                 nonlocal t_ingest, t_step
@@ -406,6 +416,7 @@ class Bench:
                     w = model.latestModel().weights.toArray()
                     t_ingest += t1 - t0
                     t_step += time.perf_counter() - t1
+                    step_ms.append((time.perf_counter() - t0) * 1e3)
                     b.free()
                     if streamed and i + 1 < k:
                         t2 = time.perf_counter()
@@ -415,6 +426,7 @@ class Bench:
 
             run(1)
             t_ingest = t_step = 0.0
+            del step_ms[:]
             self.barrier()
             t0 = time.perf_counter()
             st, w = run(e2e_steps)
@@ -423,9 +435,11 @@ class Bench:
             assert st["batch"] >= n and np.all(np.isfinite(w))
             e2e = {"value": world * n * iters * e2e_steps / e2e_s, "unit": UNIT,
                    "h2d_bytes_per_step": int(world * h2d),
+                   **({"host_input_bytes_per_step": int(world * host_input)} if tweets is not None else {}),
                    "d2h_bytes_per_step": int(world * (d * 8 + iters * 8 + 80)),
                    "steps": e2e_steps, "ingest_ms_per_step": t_ingest / e2e_steps * 1e3,
                    "compute_ms_per_step": t_step / e2e_steps * 1e3,
+                   "step_ms": [round(x, 3) for x in step_ms[:64]],   # this rank's wall clock per step (ingest call + step)
                    "h2d_GBps_effective_per_gpu": h2d * e2e_steps / e2e_s / 1e9,
                    "overlap": "none: HBM holds one batch of this size, ingest and compute alternate" if streamed else
                               ("none (--e2e-sync)" if self.args.e2e_sync else "step t+1's ingest runs beside step t's compute"),

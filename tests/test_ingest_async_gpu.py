@@ -76,6 +76,34 @@ def test_tweets_async_equals_blocking(tw, ctx, n, F):
     ba.free()
 
 
+@pytest.mark.parametrize("shift", [0, 1, 3, 8])
+@pytest.mark.parametrize("window", [(100, 1000), (1, 10 ** 6)])
+def test_tweet_text_read_in_place_from_page_locked_memory(tw, ctx, oracle, shift, window):
+    """When few tweets pass the filter and the text column is page-locked, the featuriser reads the kept tweets' text where
+    it lies (no copy of the column); with many kept tweets the column is copied.  Either way, and at every alignment of the
+    column's first unit, the CSR is the restatement's, byte for byte."""
+    from test_sparse_gpu import synth_tweets
+    t, now = synth_tweets(6000, seed=900 + shift)
+    tb = tw.TweetBatch(t["texts"], t["retweet_count"], t["followers"], t["favourites"], t["friends"], t["created_ms"], t["is_retweet"])
+    ref = oracle.featurize(tb.text_utf16, tb.text_off, tb.retweet_count, tb.followers, tb.favourites, tb.friends,
+                           tb.created_ms, tb.is_retweet, now, window[0], window[1], 1000)
+    room = pinned(np.zeros(tb.text_utf16.size + shift + 8, np.uint16))
+    text = room[shift:shift + tb.text_utf16.size]
+    text[:] = tb.text_utf16
+    room[:shift] = 0xFFFF                                    # units next to the column that must never be looked at
+    room[shift + tb.text_utf16.size:] = 0xFFFF
+    cols = [pinned(a) for a in (tb.text_off, tb.retweet_count, tb.followers, tb.favourites, tb.friends, tb.created_ms, tb.is_retweet)]
+    ptb = tw.TweetBatch.from_arrays(text, *cols)
+    assert ptb.text_utf16.ctypes.data == text.ctypes.data   # no copy on the way in
+    for make in (ctx.batch_from_tweets, ctx.batch_from_tweets_async):
+        b = make(ptb, now, window[0], window[1], 1000)
+        got = b.export_csr()
+        assert b.count() == len(ref[3])
+        for a, r in zip(got, ref):
+            assert a.dtype == r.dtype and np.array_equal(a, r)
+        b.free()
+
+
 @pytest.mark.parametrize("pin", [True, False])
 def test_dense_rows_appended_in_pieces(tw, ctx, oracle, pin):
     n, d = 20011, 1004

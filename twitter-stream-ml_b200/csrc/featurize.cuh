@@ -52,12 +52,33 @@ static __global__ void __launch_bounds__(kFeatWarps * 32) k_feat_terms(TweetCols
         const long long o = tw.off[i];
         const int L = (int)(tw.off[i + 1] - o);
         const int m = L >= 2 ? L - 1 : L; // sliding(2): L-1 bigrams; a 1-unit text is one short term
+        // The text of this tweet into shared memory first, with 16-byte loads over its aligned middle: tw.text may be
+        // the caller's page-locked host buffer read in place over the host link (twtml_sparse.cu tweets_ingest), where
+        // the size of a request is what the throughput depends on; no byte outside [o, o + L) is touched.
+        unsigned short* txt = reinterpret_cast<unsigned short*>(s); // (s is free until the rank sort below)
+        {
+            const uint16_t* tp = tw.text + o;
+            int head = (int)(((16u - (unsigned)(reinterpret_cast<uintptr_t>(tp) & 15u)) & 15u) >> 1);
+            head = min(head, L);
+            const int body = (L - head) >> 3, tail0 = head + 8 * body;
+            if (lane < head) txt[lane] = tp[lane];
+            for (int c = lane; c < body; c += 32) {
+                const uint4 v = *reinterpret_cast<const uint4*>(tp + head + 8 * c);
+                unsigned short* q = txt + head + 8 * c;
+                q[0] = (unsigned short)(v.x & 0xffffu); q[1] = (unsigned short)(v.x >> 16);
+                q[2] = (unsigned short)(v.y & 0xffffu); q[3] = (unsigned short)(v.y >> 16);
+                q[4] = (unsigned short)(v.z & 0xffffu); q[5] = (unsigned short)(v.z >> 16);
+                q[6] = (unsigned short)(v.w & 0xffffu); q[7] = (unsigned short)(v.w >> 16);
+            }
+            if (lane < L - tail0) txt[tail0 + lane] = tp[tail0 + lane];
+        }
+        __syncwarp();
         for (int p = lane; p < m; p += 32) {
-            unsigned c0 = tw.text[o + p];
+            unsigned c0 = txt[p];
             if (lower) c0 = lower[c0];
             unsigned hv = c0; // String.hashCode of one unit
             if (L >= 2) {
-                unsigned c1 = tw.text[o + p + 1];
+                unsigned c1 = txt[p + 1];
                 if (lower) c1 = lower[c1];
                 hv = 31u * c0 + c1; // <= 2 097 120: never negative, so nonNegativeMod is a plain %
             }

@@ -7,6 +7,8 @@
 #include <condition_variable>
 #include <deque>
 #include <functional>
+#include <map>
+#include <unordered_map>
 #include <future>
 #include <mutex>
 #include <string>
@@ -52,6 +54,7 @@ struct IngestLane {
     std::mutex mu;                             // held while work is being enqueued on the lane (caller thread or the ingest worker)
     cudaStream_t stream = nullptr;
     DevBuf scan_tmp, sort_tmp;                 // CUB temporaries (prefix sums, the transpose's radix sort)
+    DevBuf feat_arena;                         // the featuriser's scratch arrays (tweet columns, terms, scans): kept from interval to interval
     DevBuf labels_tmp;                         // labels on their way into a dense batch's label column
     DevBuf stage;                              // flat landing zone of page-locked dense rows (two halves)
     cudaEvent_t stage_ev[2][2] = {};           // [half][0: chunk copied, 1: chunk spread]
@@ -76,6 +79,14 @@ struct twtml_ctx {
     cudaStream_t stream = nullptr;
     cudaStream_t copy_stream = nullptr; // asynchronous ingest (twtml_batch_from_dense_async)
     cudaMemPool_t pool = nullptr;       // batch memory: stream-ordered, kept across batches (no OS round trip, no device-wide sync)
+    // The arrays of CSR batches: blocks kept by this context and handed out again only once nothing on the device can still
+    // touch them (batch_free_locked returns them after the compute stream and the batch's own ingest are done), so a block
+    // carries no stream ordering at all.  The ingest lane allocates these arrays and the compute side frees them; through
+    // the stream-ordered pool that cross-stream reuse made the lane's allocation wait for whatever the compute stream
+    // had queued -- the training call beside it (twtml.cu block_alloc).
+    std::mutex block_mu;
+    std::multimap<size_t, void*> block_free;          // size -> idle block
+    std::unordered_map<void*, size_t> block_live;     // block in use -> size
     ncclComm_t comm = nullptr;
     std::mutex mu;
     std::atomic<int> live_handles{0}; // models + batches created on this context and not yet freed
@@ -179,6 +190,8 @@ int prepare_compute(twtml_model* m, const twtml_batch* b, bool per_row_outputs);
 // batch memory from the context's pool, ordered on the compute stream
 int pool_alloc(twtml_ctx* ctx, void** p, size_t bytes, cudaStream_t stream = nullptr);
 void pool_free(twtml_ctx* ctx, void* p, cudaStream_t stream = nullptr);
+int block_alloc(twtml_ctx* ctx, void** p, size_t bytes);   // for memory that is freed with block_release only
+void block_release(twtml_ctx* ctx, void* p);               // p must be idle on the device; pool memory is passed on to pool_free
 // launch shape of the dense iteration kernel for a feature width
 struct DenseCfg {
     int cp, c2, c2p, rl, R, nstages, grid_per_sm;

@@ -6,7 +6,6 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
-#include <chrono>
 #include <cstring>
 #include <functional>
 #include <thread>
@@ -341,6 +340,7 @@ int pool_alloc(twtml_ctx* ctx, void** p, size_t bytes, cudaStream_t stream)
         cudaGetLastError();
         cudaStreamSynchronize(stream);
         cudaMemPoolTrimTo(ctx->pool, 0);
+        { std::lock_guard<std::mutex> lk(ctx->block_mu); for (auto& kv : ctx->block_free) cudaFree(kv.second); ctx->block_free.clear(); }
         e = cudaMallocFromPoolAsync(p, bytes, ctx->pool, stream);
     }
     if (e != cudaSuccess) {
@@ -354,6 +354,66 @@ int pool_alloc(twtml_ctx* ctx, void** p, size_t bytes, cudaStream_t stream)
 void pool_free(twtml_ctx* ctx, void* p, cudaStream_t stream)
 {
     if (p) cudaFreeAsync(p, stream ? stream : ctx->stream);
+}
+
+// Sizes are rounded up to an eighth of their leading power of two (at least 2 MiB), so that the intervals of a stream,
+// which differ a little in size, find each other's blocks; a block up to twice the wanted size is accepted.
+static size_t block_size_class(size_t bytes)
+{
+    size_t lead = (size_t)1 << 21;
+    while (lead * 2 <= bytes) lead *= 2;
+    const size_t granule = std::max<size_t>((size_t)1 << 21, lead / 8);
+    return (std::max<size_t>(bytes, 1) + granule - 1) / granule * granule;
+}
+
+static void block_trim(twtml_ctx* ctx) // caller holds block_mu
+{
+    for (auto& kv : ctx->block_free) cudaFree(kv.second);
+    ctx->block_free.clear();
+}
+
+int block_alloc(twtml_ctx* ctx, void** p, size_t bytes)
+{
+    *p = nullptr;
+    const size_t want = block_size_class(bytes);
+    std::lock_guard<std::mutex> lk(ctx->block_mu);
+    auto it = ctx->block_free.lower_bound(want);
+    if (it != ctx->block_free.end() && it->first <= 2 * want) {
+        *p = it->second;
+        ctx->block_live[*p] = it->first;
+        ctx->block_free.erase(it);
+        return 0;
+    }
+    cudaSetDevice(ctx->device);
+    cudaError_t e = cudaMalloc(p, want);
+    if (e != cudaSuccess) { // give the idle blocks and the pool's cached memory back and try once more
+        cudaGetLastError();
+        block_trim(ctx);
+        cudaMemPoolTrimTo(ctx->pool, 0);
+        e = cudaMalloc(p, want);
+    }
+    if (e != cudaSuccess) {
+        *p = nullptr;
+        cudaGetLastError();
+        return fail(TWTML_E_OOM, "device allocation of %zu bytes: %s", want, cudaGetErrorString(e));
+    }
+    ctx->block_live[*p] = want;
+    return 0;
+}
+
+void block_release(twtml_ctx* ctx, void* p)
+{
+    if (!p) return;
+    {
+        std::lock_guard<std::mutex> lk(ctx->block_mu);
+        auto it = ctx->block_live.find(p);
+        if (it != ctx->block_live.end()) {
+            ctx->block_free.emplace(it->second, p);
+            ctx->block_live.erase(it);
+            return;
+        }
+    }
+    pool_free(ctx, p); // not one of ours: stream-ordered pool memory (dense batches)
 }
 
 static int ensure_pinned(IngestLane& lane, size_t bytes)
@@ -1020,6 +1080,7 @@ int prepare_compute(twtml_model* m, const twtml_batch* b, bool per_row_outputs)
 void batch_free_locked(twtml_batch* b)
 {
     if (b->has_pending) b->pending.wait(); // the worker still owns its fields
+    if (b->has_pending && b->pending.get() != 0) cudaStreamSynchronize(b->ctx->copy_stream); // a failed ingest: its kernels may still run, its event was never recorded
     if (b->ready) {
         cudaEventSynchronize(b->ready); // its own copy only; later batches may still be arriving
         cudaEventDestroy(b->ready);
@@ -1028,7 +1089,7 @@ void batch_free_locked(twtml_batch* b)
     for (void* p : {(void*)b->X, (void*)b->rowptr, (void*)b->colidx, (void*)b->vals, (void*)b->labels, (void*)b->colptr, (void*)b->rowidx,
                     (void*)b->cvals, (void*)b->headbits, (void*)b->nzcol, (void*)b->win_first_nz, (void*)b->wkey, (void*)b->win_first_part,
                     (void*)b->win_last_part, (void*)b->diff, (void*)b->bounds, (void*)b->pcolidx, (void*)b->pvals})
-        pool_free(b->ctx, p);
+        block_release(b->ctx, p); // (the compute stream and the batch's own ingest are done: the arrays are idle)
     b->ctx->live_handles -= 1;
     delete b;
 }
@@ -1163,7 +1224,7 @@ int32_t twtml_destroy(twtml_ctx* ctx)
                       &ctx->tmp_a, &ctx->tmp_b, &ctx->gather, &ctx->lower, &ctx->upd_parts, &ctx->slices, &ctx->wprev})
         b->release();
     for (auto& lane : ctx->lane) {
-        for (DevBuf* b : {&lane.scan_tmp, &lane.sort_tmp, &lane.labels_tmp, &lane.stage}) b->release();
+        for (DevBuf* b : {&lane.scan_tmp, &lane.sort_tmp, &lane.labels_tmp, &lane.stage, &lane.feat_arena}) b->release();
         for (int i = 0; i < 2; ++i) {
             if (lane.pin[i]) cudaFreeHost(lane.pin[i]);
             if (lane.pin_ev[i]) cudaEventDestroy(lane.pin_ev[i]);
@@ -1173,6 +1234,13 @@ int32_t twtml_destroy(twtml_ctx* ctx)
                 if (ev) cudaEventDestroy(ev);
     }
     for (cudaEvent_t e : ctx->ev) cudaEventDestroy(e);
+    {
+        std::lock_guard<std::mutex> lk(ctx->block_mu);
+        for (auto& kv : ctx->block_free) cudaFree(kv.second);
+        for (auto& kv : ctx->block_live) cudaFree(kv.first);
+        ctx->block_free.clear();
+        ctx->block_live.clear();
+    }
     if (ctx->pool) cudaMemPoolDestroy(ctx->pool);
     cudaStreamDestroy(ctx->stream);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);

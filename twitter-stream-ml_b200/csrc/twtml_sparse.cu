@@ -11,12 +11,14 @@
 #include <cstring>
 #include <mutex>
 #include <thread>
+#include <type_traits>
 #include <vector>
 
 #include "csr.cuh"
 #include "csr_narrow.cuh"
 #include "featurize.cuh"
 #include "host.h"
+#include <chrono>
 #include "lower_table.h"
 #include "reduce.cuh"
 #include "synth.cuh"
@@ -27,6 +29,13 @@ template <class T>
 static int dev_alloc(twtml_ctx* ctx, IngestLane& lane, T** p, size_t count)
 {
     return pool_alloc(ctx, reinterpret_cast<void**>(p), sizeof(T) * std::max<size_t>(count, 1), lane.stream);
+}
+
+// an array that belongs to the batch (given back by batch_free_locked): a block of the context, free of stream ordering
+template <class T>
+static int batch_array(twtml_ctx* ctx, T** p, size_t count)
+{
+    return block_alloc(ctx, reinterpret_cast<void**>(p), sizeof(T) * std::max<size_t>(count, 1));
 }
 
 static int exclusive_sum(IngestLane& lane, const long long* in, long long* out, long long n)
@@ -52,13 +61,13 @@ static int csr_finalize_narrow(twtml_ctx* ctx, IngestLane& lane, twtml_batch* b)
     if (warps < 4) return 1;
     // one partial vector per CTA of a grid fixed here: the plan's "blocks" are those CTAs
     const long long grid = std::max<long long>(1, std::min<long long>((n + warps - 1) / warps, (long long)ctx->sm_count));
-    TW_TRY(dev_alloc(ctx, lane, &b->bounds, (size_t)grid + 1));
+    TW_TRY(batch_array(ctx, &b->bounds, (size_t)grid + 1));
     k_narrow_bounds<<<blocks_for(grid + 1, 256), 256, 0, lane.stream>>>(b->rowptr, n, grid, b->bounds);
     TW_CUDA(cudaGetLastError());
     static const bool no_permute = getenv("TWTML_NO_NARROW_PERMUTE") != nullptr; // A/B switch
     if (!no_permute && b->nnz > 0) { // the kernel's own copy of the entries, laid out against shared-memory bank conflicts
-        TW_TRY(dev_alloc(ctx, lane, &b->pcolidx, (size_t)b->nnz + kNarrowSlack));
-        TW_TRY(dev_alloc(ctx, lane, &b->pvals, (size_t)b->nnz + kNarrowSlack));
+        TW_TRY(batch_array(ctx, &b->pcolidx, (size_t)b->nnz + kNarrowSlack));
+        TW_TRY(batch_array(ctx, &b->pvals, (size_t)b->nnz + kNarrowSlack));
         const unsigned pg = (unsigned)std::min<long long>((n + 7) / 8, (long long)ctx->sm_count * 16);
         k_narrow_permute<<<std::max(1u, pg), 256, 0, lane.stream>>>(b->rowptr, n, b->colidx, b->vals, b->pcolidx, b->pvals);
         TW_CUDA(cudaGetLastError());
@@ -93,16 +102,16 @@ static int csr_finalize(twtml_ctx* ctx, IngestLane& lane, twtml_batch* b, bool d
     const long long nnz = b->nnz;
     const long long nwin = (nnz + kWin - 1) / kWin;
     b->nwin = nwin;
-    TW_TRY(dev_alloc(ctx, lane, &b->colptr, (size_t)d + 1));
-    TW_TRY(dev_alloc(ctx, lane, &b->rowidx, (size_t)nnz));
-    TW_TRY(dev_alloc(ctx, lane, &b->cvals, (size_t)nnz));
-    TW_TRY(dev_alloc(ctx, lane, &b->diff, (size_t)b->n));
-    TW_TRY(dev_alloc(ctx, lane, &b->headbits, (size_t)(nwin + 1) * 8));
-    TW_TRY(dev_alloc(ctx, lane, &b->win_first_nz, (size_t)nwin + 1));
-    TW_TRY(dev_alloc(ctx, lane, &b->wkey, (size_t)nwin + 1));
-    TW_TRY(dev_alloc(ctx, lane, &b->win_first_part, (size_t)nwin + 1));
-    TW_TRY(dev_alloc(ctx, lane, &b->win_last_part, (size_t)nwin + 1));
-    TW_TRY(dev_alloc(ctx, lane, &b->nzcol, (size_t)std::min<long long>(nnz, d) + 1));
+    TW_TRY(batch_array(ctx, &b->colptr, (size_t)d + 1));
+    TW_TRY(batch_array(ctx, &b->rowidx, (size_t)nnz));
+    TW_TRY(batch_array(ctx, &b->cvals, (size_t)nnz));
+    TW_TRY(batch_array(ctx, &b->diff, (size_t)b->n));
+    TW_TRY(batch_array(ctx, &b->headbits, (size_t)(nwin + 1) * 8));
+    TW_TRY(batch_array(ctx, &b->win_first_nz, (size_t)nwin + 1));
+    TW_TRY(batch_array(ctx, &b->wkey, (size_t)nwin + 1));
+    TW_TRY(batch_array(ctx, &b->win_first_part, (size_t)nwin + 1));
+    TW_TRY(batch_array(ctx, &b->win_last_part, (size_t)nwin + 1));
+    TW_TRY(batch_array(ctx, &b->nzcol, (size_t)std::min<long long>(nnz, d) + 1));
     TW_CUDA(cudaMemsetAsync(b->headbits, 0, sizeof(unsigned) * (size_t)(nwin + 1) * 8, st));
     if (nnz > 0) {
         int *keys_out = nullptr, *iota = nullptr, *perm = nullptr;
@@ -161,10 +170,10 @@ static twtml_batch* csr_shell(twtml_ctx* ctx, int64_t n, int64_t d, int64_t nnz)
 static int csr_alloc(twtml_ctx* ctx, IngestLane& lane, twtml_batch* b)
 {
     // colidx / vals end in kNarrowSlack spare entries: the narrow kernel's bulk copies are 16 bytes wide
-    TW_TRY(dev_alloc(ctx, lane, &b->rowptr, (size_t)b->n + 1));
-    TW_TRY(dev_alloc(ctx, lane, &b->colidx, (size_t)b->nnz + kNarrowSlack));
-    TW_TRY(dev_alloc(ctx, lane, &b->vals, (size_t)b->nnz + kNarrowSlack));
-    TW_TRY(dev_alloc(ctx, lane, &b->labels, (size_t)b->n));
+    TW_TRY(batch_array(ctx, &b->rowptr, (size_t)b->n + 1));
+    TW_TRY(batch_array(ctx, &b->colidx, (size_t)b->nnz + kNarrowSlack));
+    TW_TRY(batch_array(ctx, &b->vals, (size_t)b->nnz + kNarrowSlack));
+    TW_TRY(batch_array(ctx, &b->labels, (size_t)b->n));
     return 0;
 }
 
@@ -401,6 +410,19 @@ static int tweets_precheck(const TweetArgs& t, int64_t* n_kept)
     return 0;
 }
 
+// The address under which the current device can read [p, p + bytes) of the caller's host memory, or null when that memory
+// is not page-locked / not mapped for this device.
+static const void* device_alias(const void* p, size_t bytes)
+{
+    cudaPointerAttributes first{}, last{};
+    void* dp = nullptr;
+    const bool ok = bytes > 0 && cudaPointerGetAttributes(&first, p) == cudaSuccess && first.type == cudaMemoryTypeHost &&
+                    cudaPointerGetAttributes(&last, static_cast<const char*>(p) + bytes - 1) == cudaSuccess && last.type == cudaMemoryTypeHost &&
+                    cudaHostGetDevicePointer(&dp, const_cast<void*>(p), 0) == cudaSuccess && dp != nullptr;
+    cudaGetLastError();
+    return ok ? dp : nullptr;
+}
+
 static int tweets_ingest(twtml_ctx* ctx, IngestLane& lane, twtml_batch* b, const TweetArgs& t, bool defer_global)
 {
     std::lock_guard<std::mutex> lane_lock(lane.mu);
@@ -420,60 +442,109 @@ static int tweets_ingest(twtml_ctx* ctx, IngestLane& lane, twtml_batch* b, const
     long long *d_off = nullptr, *d_created = nullptr, *keep = nullptr, *rownnz = nullptr, *krow = nullptr, *eoff = nullptr;
     int *d_rc = nullptr, *d_fo = nullptr, *d_fa = nullptr, *d_fr = nullptr, *pair_idx = nullptr, *pair_cnt = nullptr;
     uint8_t* d_rt = nullptr;
-    std::vector<void*> owned;
-    auto cleanup = [&]() { for (void* p : owned) pool_free(ctx, p, st); };
-#define TW_OWN(call, ptrvar) do { int rc_ = (call); if (rc_) { cleanup(); return rc_; } owned.push_back(ptrvar); } while (0)
-#define TW_DO(call) do { int rc_ = (call); if (rc_) { cleanup(); return rc_; } } while (0)
-    TW_OWN(dev_alloc(ctx, lane, &d_text, (size_t)units), d_text);
-    TW_OWN(dev_alloc(ctx, lane, &d_off, (size_t)n + 1), d_off);
-    TW_OWN(dev_alloc(ctx, lane, &d_created, (size_t)n), d_created);
-    TW_OWN(dev_alloc(ctx, lane, &d_rc, (size_t)n), d_rc);
-    TW_OWN(dev_alloc(ctx, lane, &d_fo, (size_t)n), d_fo);
-    TW_OWN(dev_alloc(ctx, lane, &d_fa, (size_t)n), d_fa);
-    TW_OWN(dev_alloc(ctx, lane, &d_fr, (size_t)n), d_fr);
-    TW_OWN(dev_alloc(ctx, lane, &d_rt, (size_t)n), d_rt);
-    TW_OWN(dev_alloc(ctx, lane, &pair_idx, (size_t)units), pair_idx);
-    TW_OWN(dev_alloc(ctx, lane, &pair_cnt, (size_t)units), pair_cnt);
-    TW_OWN(dev_alloc(ctx, lane, &keep, (size_t)n + 1), keep);
-    TW_OWN(dev_alloc(ctx, lane, &rownnz, (size_t)n + 1), rownnz);
-    TW_OWN(dev_alloc(ctx, lane, &krow, (size_t)n + 1), krow);
-    TW_OWN(dev_alloc(ctx, lane, &eoff, (size_t)n + 1), eoff);
-    if (units) TW_DO(upload_plain(ctx, lane, d_text, t.text_utf16, sizeof(uint16_t) * (size_t)units));
+#define TW_DO(call) do { int rc_ = (call); if (rc_) return rc_; } while (0)
+    // TWTML_TRACE_INGEST=1: where one ingest spends its time, on the device (events on the lane's stream) and on this thread
+    static const bool trace = getenv("TWTML_TRACE_INGEST") != nullptr;
+    cudaEvent_t tev[6] = {};
+    const auto h0 = std::chrono::steady_clock::now();
+    double hms[16] = {};
+    auto mark = [&](int k) { if (trace) { if (!tev[k]) cudaEventCreate(&tev[k]); cudaEventRecord(tev[k], st); } };
+    auto hmark = [&](int k) { hms[k] = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - h0).count(); };
+    // The text of a tweet is needed only if the tweet passes the filter, and the filter does not look at it.  When
+    // few tweets pass and the caller's text is page-locked memory this device can address, the featuriser reads the
+    // kept tweets' text in place over the host link and the text column is not copied at all (10^6 tweets, 14 % kept:
+    // ~20 MB cross the link instead of 140 MB).  b->n is the host filter's count of kept tweets.
+    static const bool no_in_place = getenv("TWTML_NO_TEXT_IN_PLACE") != nullptr; // A/B switch
+    const uint16_t* text_in_place = nullptr;
+    if (units && !no_in_place && b->n * 2 <= n) text_in_place = static_cast<const uint16_t*>(device_alias(t.text_utf16, sizeof(uint16_t) * (size_t)units));
+    // The scratch arrays live in one buffer of the lane that is kept from interval to interval (it grows to the largest
+    // interval seen): no allocator call per interval.
+    auto al = [](size_t bytes) { return (std::max<size_t>(bytes, 1) + 255) & ~(size_t)255; };
+    const size_t un = (size_t)units, nn = (size_t)n;
+    const size_t total = (text_in_place ? 0 : al(2 * un)) + 5 * al(8 * (nn + 1)) + al(8 * nn) + 4 * al(4 * nn) + al(nn) + 2 * al(4 * un);
+    TW_TRY(lane.feat_arena.reserve(total));
+    size_t arena_off = 0;
+    auto carve = [&](auto** p, size_t count) -> int {
+        using T = std::remove_pointer_t<std::remove_pointer_t<decltype(p)>>;
+        *p = reinterpret_cast<T*>(lane.feat_arena.as<char>() + arena_off);
+        arena_off += al(sizeof(T) * count);
+        return arena_off <= lane.feat_arena.cap ? 0 : fail(TWTML_E_CUDA, "featuriser scratch overrun");
+    };
+    if (!text_in_place) TW_DO(carve(&d_text, un));
+    TW_DO(carve(&d_off, nn + 1));
+    TW_DO(carve(&d_created, nn));
+    TW_DO(carve(&d_rc, nn));
+    TW_DO(carve(&d_fo, nn));
+    TW_DO(carve(&d_fa, nn));
+    TW_DO(carve(&d_fr, nn));
+    TW_DO(carve(&d_rt, nn));
+    TW_DO(carve(&pair_idx, un));
+    TW_DO(carve(&pair_cnt, un));
+    TW_DO(carve(&keep, nn + 1));
+    TW_DO(carve(&rownnz, nn + 1));
+    TW_DO(carve(&krow, nn + 1));
+    TW_DO(carve(&eoff, nn + 1));
+    hmark(3);
+    mark(0);
+    hmark(8);
+    if (units && !text_in_place) TW_DO(upload_plain(ctx, lane, d_text, t.text_utf16, sizeof(uint16_t) * (size_t)units));
     TW_DO(upload_plain(ctx, lane, d_off, t.text_off, sizeof(int64_t) * (size_t)(n + 1)));
+    hmark(6);
     TW_DO(upload_plain(ctx, lane, d_created, t.created_ms, sizeof(int64_t) * (size_t)n));
+    hmark(9);
     TW_DO(upload_plain(ctx, lane, d_rc, t.retweet_cnt, sizeof(int32_t) * (size_t)n));
+    hmark(10);
     TW_DO(upload_plain(ctx, lane, d_fo, t.followers, sizeof(int32_t) * (size_t)n));
     TW_DO(upload_plain(ctx, lane, d_fa, t.favourites, sizeof(int32_t) * (size_t)n));
     TW_DO(upload_plain(ctx, lane, d_fr, t.friends, sizeof(int32_t) * (size_t)n));
     TW_DO(upload_plain(ctx, lane, d_rt, t.is_retweet, (size_t)n));
 
+    hmark(4);
     const uint16_t* lower = nullptr;
     if (t.flags & TWTML_FLAG_LOWERCASE) TW_DO(lower_table(ctx, &lower));
-    TweetCols tc{d_text, d_off, d_rc, d_fo, d_fa, d_fr, d_created, d_rt};
+    TweetCols tc{text_in_place ? text_in_place : d_text, d_off, d_rc, d_fo, d_fa, d_fr, d_created, d_rt};
     cudaMemsetAsync(keep + n, 0, sizeof(long long), st);
     cudaMemsetAsync(rownnz + n, 0, sizeof(long long), st);
-    const unsigned gridA = (unsigned)std::min<long long>((n + kFeatWarps - 1) / kFeatWarps, (long long)ctx->sm_count * 16);
+    mark(1);
+    const long long cta_cap = (long long)ctx->sm_count * 16;
+    const unsigned gridA = (unsigned)std::min<long long>((n + kFeatWarps - 1) / kFeatWarps, cta_cap);
     k_feat_terms<<<gridA, kFeatWarps * 32, 0, st>>>(tc, n, t.rt_begin, t.rt_end, F, lower, pair_idx, pair_cnt, keep, rownnz);
+    hmark(5);
+    mark(2);
     TW_DO(exclusive_sum(lane, keep, krow, n + 1));
     TW_DO(exclusive_sum(lane, rownnz, eoff, n + 1));
+    mark(3);
+    hmark(0);
     // the one size only the device knows: how many entries the kept rows have (the row count was settled on the host)
     long long tot[2] = {0, 0};
     cudaMemcpyAsync(&tot[0], krow + n, sizeof(long long), cudaMemcpyDeviceToHost, st);
     cudaMemcpyAsync(&tot[1], eoff + n, sizeof(long long), cudaMemcpyDeviceToHost, st);
-    if (cudaStreamSynchronize(st) != cudaSuccess) { cleanup(); return fail(TWTML_E_CUDA, "featuriser failed: %s", cudaGetErrorString(cudaGetLastError())); }
-    if (tot[0] != b->n) { cleanup(); return fail(TWTML_E_CUDA, "featuriser kept %lld rows, the host filter %lld", tot[0], (long long)b->n); }
+    if (cudaStreamSynchronize(st) != cudaSuccess) return fail(TWTML_E_CUDA, "featuriser failed: %s", cudaGetErrorString(cudaGetLastError()));
+    if (tot[0] != b->n) { return fail(TWTML_E_CUDA, "featuriser kept %lld rows, the host filter %lld", tot[0], (long long)b->n); }
     b->nnz = tot[1];
+    hmark(1);
     TW_DO(csr_alloc(ctx, lane, b));
-    const unsigned gridB = (unsigned)std::min<long long>((n + 3) / 4, (long long)ctx->sm_count * 16);
+    const unsigned gridB = (unsigned)std::min<long long>((n + 3) / 4, cta_cap);
     k_feat_pack<<<gridB, 128, 0, st>>>(tc, n, t.now_ms, F, pair_idx, pair_cnt, keep, krow, rownnz, eoff, b->rowptr, b->colidx, b->vals, b->labels);
     cudaError_t e = cudaGetLastError();
     if (e == cudaSuccess) e = cudaMemcpyAsync(b->rowptr + b->n, eoff + n, sizeof(long long), cudaMemcpyDeviceToDevice, st);
-    cleanup();
-#undef TW_OWN
 #undef TW_DO
     if (e != cudaSuccess) return fail(TWTML_E_CUDA, "featuriser pack failed: %s", cudaGetErrorString(e));
+    mark(4);
     TW_TRY(csr_finalize(ctx, lane, b, defer_global));
+    mark(5);
     if (b->ready) TW_CUDA(cudaEventRecord(b->ready, st));
+    if (trace) {
+        hmark(2);
+        cudaStreamSynchronize(st);
+        float d[5] = {};
+        for (int k = 0; k < 5; ++k) cudaEventElapsedTime(&d[k], tev[k], tev[k + 1]);
+        const double hend = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - h0).count();
+        fprintf(stderr, "[twtml ingest] device ms: copies %.3f  terms %.3f  scans %.3f  sync+pack %.3f  finalize %.3f | host ms: allocs %.3f  first copy %.3f  copies %.3f  terms %.3f  scans %.3f  sizes back %.3f  all enqueued %.3f  done %.3f\n",
+                d[0], d[1], d[2], d[3], d[4], hms[3], hms[6], hms[4], hms[5], hms[0], hms[1], hms[2], hend);
+        fprintf(stderr, "[twtml ingest]   host ms: allocs %.3f  event %.3f  copy1 %.3f  copy2 %.3f  copy3 %.3f  all copies %.3f\n", hms[3], hms[8], hms[6], hms[9], hms[10], hms[4]);
+        for (int k = 0; k < 6; ++k) cudaEventDestroy(tev[k]);
+    }
     return 0;
 }
 
