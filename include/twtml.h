@@ -153,7 +153,12 @@ int32_t twtml_num_features(const twtml_model* m, int64_t* d);
  *  now_ms: System.currentTimeMillis at MllibHelper.scala:61, injected.
  *  rt_begin/rt_end: numRetweetBegin/End (MllibHelper.scala:15-16), both inclusive.
  * The batch is CSR of width num_text_features + 4; rows failing the filter are dropped,
- * order kept.  n may be 0. */
+ * order kept.  n may be 0.
+ * Only tweets that pass the filter are featurised (featurize runs after filtrate, :44-46), and the
+ * filter does not look at the text.  When at most half of the tweets pass and text_utf16 is
+ * page-locked host memory the device can address (cudaHostAlloc / cudaHostRegister), the text column
+ * is therefore not copied: the featuriser reads the kept tweets' text where it lies, over the host
+ * link.  Same result, byte for byte; pageable text is copied as before. */
 #define TWTML_FLAG_LOWERCASE 1u
 int32_t twtml_batch_from_tweets(twtml_ctx* ctx, const uint16_t* text_utf16, const int64_t* text_off,
                                 const int32_t* retweet_cnt, const int32_t* followers,
