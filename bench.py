@@ -21,6 +21,10 @@ The JSON line is the default workload's; at N = 1 it also carries "sub_records" 
 (value, roofline, e2e) for dense_1m, tweets_1m and csr_2m (--sub none turns them off).
 Multi-GPU: every rank holds the same number of rows (weak scaling); per iteration the ranks exchange
 their (gradSum, lossSum, count) shard vectors (peer-memory stores, NCCL as the fallback).
+The "e2e" object also carries "step_ms", this rank's wall clock of every end-to-end step (a stall shows there, not in
+the mean).  For tweets, "h2d_bytes_per_step" counts what crosses the host link -- the copied columns plus the text of the
+tweets that pass the filter, which the featuriser reads in place from the page-locked column -- and
+"host_input_bytes_per_step" the whole input as it lies in host memory.
 """
 import argparse
 import json
